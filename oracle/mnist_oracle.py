@@ -1,0 +1,168 @@
+"""CPU oracle for the examples/mnist training step and the examples/smoke-dist check.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``pytorch-operator_b200/`` may import this
+module; only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` legs do.  It is a restatement, on
+``torch`` CPU ops, of what the reference payloads compute -- the arithmetic of
+the reference lives in a third-party dependency (PyTorch; image pin
+``pytorch/pytorch:1.0-cuda10.0-cudnn7-runtime``, examples/mnist/Dockerfile:1),
+so the restatement calls the same library ops the reference calls, in the same
+order, but in functional form over an explicit parameter dict.
+
+Parity status: the reference repo holds NO numeric golden vectors for this path
+("parity unpinned" by the reference's own tests).  This
+oracle is pinned instead against outputs of the reference itself, run in the
+build container: ``oracle/gen_golden.py`` imports the unmodified
+``/root/reference/examples/mnist/mnist.py`` (``Net``, ``train``) and
+``examples/smoke-dist/dist_sendrecv.py`` (``run``) and writes
+``tests/golden/*.npz``; ``tests/test_oracle.py`` checks every function here
+against those files.
+"""
+from __future__ import annotations
+
+import math
+from collections import OrderedDict
+
+import torch
+import torch.nn.functional as F
+
+# Parameter names/shapes in declaration order (examples/mnist/mnist.py:20-23).
+PARAM_SHAPES = OrderedDict([
+    ("conv1.weight", (20, 1, 5, 5)), ("conv1.bias", (20,)),
+    ("conv2.weight", (50, 20, 5, 5)), ("conv2.bias", (50,)),
+    ("fc1.weight", (500, 800)), ("fc1.bias", (500,)),
+    ("fc2.weight", (10, 500)), ("fc2.bias", (10,)),
+])
+N_PARAMS = sum(math.prod(s) for s in PARAM_SHAPES.values())  # 431,080
+
+
+def init_params(seed: int = 1) -> "OrderedDict[str, torch.Tensor]":
+    """Initial parameters the reference gets from ``torch.manual_seed(seed); Net()``
+    (mnist.py:110,133 with Net.__init__ at :17-23): nn.Conv2d / nn.Linear default
+    init is kaiming_uniform_(a=sqrt(5)) on the weight then U(-1/sqrt(fan_in), +) on
+    the bias, layer by layer in declaration order.  Restated with the raw init
+    calls so the RNG stream is consumed identically."""
+    gen_state = torch.random.get_rng_state()
+    torch.manual_seed(seed)
+    out = OrderedDict()
+    names = list(PARAM_SHAPES)
+    for wname, bname in zip(names[0::2], names[1::2]):
+        w = torch.empty(PARAM_SHAPES[wname])
+        torch.nn.init.kaiming_uniform_(w, a=math.sqrt(5))
+        fan_in = math.prod(PARAM_SHAPES[wname][1:])
+        bound = 1.0 / math.sqrt(fan_in)
+        b = torch.empty(PARAM_SHAPES[bname])
+        torch.nn.init.uniform_(b, -bound, bound)
+        out[wname], out[bname] = w, b
+    torch.random.set_rng_state(gen_state)
+    return out
+
+
+def synthetic_batch(batch_size: int, seed: int):
+    """Seeded synthetic batch: randn images at normalised-MNIST scale,
+    int64 labels in [0,10) drawn from the same generator."""
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(batch_size, 1, 28, 28, generator=g)
+    t = torch.randint(0, 10, (batch_size,), generator=g)
+    return x, t
+
+
+def forward(params, x: torch.Tensor) -> torch.Tensor:
+    """Net.forward (mnist.py:25-33): conv5x5+ReLU, 2x2 max-pool, conv5x5+ReLU,
+    2x2 max-pool, flatten to 800, fc+ReLU, fc, log_softmax over the 10 classes."""
+    a = F.max_pool2d(F.relu(F.conv2d(x, params["conv1.weight"], params["conv1.bias"])), 2, 2)
+    a = F.max_pool2d(F.relu(F.conv2d(a, params["conv2.weight"], params["conv2.bias"])), 2, 2)
+    a = a.reshape(-1, 800)
+    a = F.relu(F.linear(a, params["fc1.weight"], params["fc1.bias"]))
+    a = F.linear(a, params["fc2.weight"], params["fc2.bias"])
+    return F.log_softmax(a, dim=1)
+
+
+def loss_and_grads(params, x, target):
+    """One forward + ``F.nll_loss`` (mean) + backward (mnist.py:40-42).  Returns
+    (loss, logp, grads) with grads keyed like params; params are not modified."""
+    leaves = OrderedDict((k, v.detach().clone().requires_grad_(True)) for k, v in params.items())
+    logp = forward(leaves, x)
+    loss = F.nll_loss(logp, target)
+    gl = torch.autograd.grad(loss, list(leaves.values()))
+    return loss.detach(), logp.detach(), OrderedDict(zip(leaves.keys(), gl))
+
+
+def sgd_momentum_(params, grads, bufs, lr=0.01, momentum=0.5):
+    """optim.SGD(lr, momentum) step with dampening 0, no nesterov, no weight decay
+    (mnist.py:140,43): first step ``buf = g``; afterwards ``buf = mu*buf + g``;
+    ``p = p - lr*buf``.  ``bufs`` is a dict that is filled on the first call."""
+    for k, p in params.items():
+        g = grads[k]
+        if k not in bufs:
+            bufs[k] = g.clone()
+        else:
+            bufs[k].mul_(momentum).add_(g)
+        p.add_(bufs[k], alpha=-lr)
+
+
+def average_grads(per_rank_grads):
+    """What DDP leaves in ``p.grad`` on every rank (mnist.py:135-138): the sum of the
+    ranks' gradients divided by world_size."""
+    ws = len(per_rank_grads)
+    out = OrderedDict()
+    for k in per_rank_grads[0]:
+        s = per_rank_grads[0][k].clone()
+        for r in range(1, ws):
+            s = s + per_rank_grads[r][k]
+        out[k] = s / ws
+    return out
+
+
+def train_steps(params, batches_per_rank, lr=0.01, momentum=0.5):
+    """Free-running restatement of ``train()`` (mnist.py:35-43) for world_size =
+    len(batches_per_rank) replicas that start identical and see per-rank batches.
+    ``batches_per_rank[r]`` is a list of (x, target).  Returns per-step
+    dicts {losses: [per-rank], grads: averaged grads} and leaves the final
+    parameters in ``params`` / momentum in the returned ``bufs``."""
+    bufs, trace = {}, []
+    nsteps = len(batches_per_rank[0])
+    for s in range(nsteps):
+        losses, grads = [], []
+        for rb in batches_per_rank:
+            l, _, g = loss_and_grads(params, *rb[s])
+            losses.append(float(l))
+            grads.append(g)
+        avg = average_grads(grads) if len(grads) > 1 else grads[0]
+        sgd_momentum_(params, avg, bufs, lr, momentum)
+        trace.append({"losses": losses, "grads": avg})
+    return trace, bufs
+
+
+def evaluate(params, x, target):
+    """One batch of ``test()`` (mnist.py:56-61): summed NLL and number of correct
+    argmax predictions."""
+    logp = forward(params, x)
+    loss_sum = float(F.nll_loss(logp, target, reduction="sum"))
+    pred = logp.max(1, keepdim=True)[1]
+    correct = int(pred.eq(target.view_as(pred)).sum())
+    return loss_sum, correct, logp
+
+
+def smoke_sendrecv(inp: torch.Tensor, world_size: int):
+    """What rank 0 receives from each worker in dist_sendrecv.py:15-34: every worker
+    returns ``torch.mul(inp, inp)`` of the tensor rank 0 sent it."""
+    return [torch.mul(inp, inp) for _ in range(1, world_size)]
+
+
+class TorchCpuTrainer:
+    """Timed CPU baseline for bench.py: the same op sequence as the reference's
+    ``train()`` body, on nn.Module-free functional torch CPU ops with autograd and
+    ``torch.optim.SGD``, so the library kernels exercised (mkldnn conv, addmm, ...)
+    are the ones the reference exercises on a CPU pod."""
+
+    def __init__(self, seed=1, lr=0.01, momentum=0.5):
+        self.params = OrderedDict((k, v.requires_grad_(True)) for k, v in init_params(seed).items())
+        self.opt = torch.optim.SGD(list(self.params.values()), lr=lr, momentum=momentum)
+
+    def step(self, x, target) -> torch.Tensor:
+        self.opt.zero_grad()
+        loss = F.nll_loss(forward(self.params, x), target)
+        loss.backward()
+        self.opt.step()
+        return loss.detach()

@@ -1,0 +1,102 @@
+"""Pins the two CPU restatements (oracle/mnist_oracle.py on torch ops, oracle/lenet_ref.c in
+plain C) against the fixtures the UNMODIFIED reference produced (oracle/gen_golden.py)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import c_oracle, mnist_oracle as mo
+from tests.helpers import NAMES, RTOL, assert_close, batch_seed, golden_tensor_check, load_golden
+
+
+def test_param_count_and_init_matches_reference():
+    gold = load_golden("train_ws1_b64")
+    params = mo.init_params(1)
+    assert mo.N_PARAMS == 431080 == sum(v.numel() for v in params.values())
+    for n in NAMES:
+        golden_tensor_check(gold, "init", n, params[n].numpy(), rtol=0.0)  # bit-exact
+
+
+@pytest.mark.parametrize("case", ["train_ws1_b64", "train_ws1_b5", "train_ws2_b64"])
+def test_torch_restatement_free_run_matches_reference(case):
+    gold = load_golden(case)
+    ws, B, nsteps = (int(gold[f"meta/{k}"][0]) for k in ("world_size", "batch_size", "nsteps"))
+    params = mo.init_params(1)
+    batches = [[mo.synthetic_batch(B, batch_seed(s, r)) for s in range(nsteps)] for r in range(ws)]
+    trace, _ = mo.train_steps(params, batches)
+    # replay again to capture params after each step
+    params = mo.init_params(1)
+    bufs = {}
+    for s in range(nsteps):
+        for r in range(ws):
+            assert abs(trace[s]["losses"][r] - float(gold[f"step{s}/loss_rank{r}"][0])) <= RTOL * 2.4
+        for n in NAMES:
+            golden_tensor_check(gold, f"step{s}/grad", n, trace[s]["grads"][n].numpy())
+        mo.sgd_momentum_(params, trace[s]["grads"], bufs)
+        for n in NAMES:
+            golden_tensor_check(gold, f"step{s}/param", n, params[n].numpy())
+
+
+@pytest.mark.parametrize("case", ["train_ws1_b64", "train_ws1_b5"])
+def test_c_restatement_step0_matches_reference(case):
+    gold = load_golden(case)
+    B = int(gold["meta/batch_size"][0])
+    params = {k: v.numpy() for k, v in mo.init_params(1).items()}
+    x, t = mo.synthetic_batch(B, batch_seed(0, 0))
+    loss, logp, grads = c_oracle.loss_and_grads(params, x.numpy(), t.numpy())
+    assert abs(loss - float(gold["step0/loss_rank0"][0])) <= RTOL * 2.4
+    for n in NAMES:
+        golden_tensor_check(gold, "step0/grad", n, grads[n])
+
+
+def test_c_and_torch_restatements_agree_ws2_average():
+    gold = load_golden("train_ws2_b64")
+    params = {k: v.numpy() for k, v in mo.init_params(1).items()}
+    gsum = None
+    for r in range(2):
+        x, t = mo.synthetic_batch(64, batch_seed(0, r))
+        loss, _, g = c_oracle.loss_and_grads(params, x.numpy(), t.numpy())
+        assert abs(loss - float(gold[f"step0/loss_rank{r}"][0])) <= RTOL * 2.4
+        gsum = g if gsum is None else {n: gsum[n] + g[n] for n in NAMES}
+    for n in NAMES:
+        golden_tensor_check(gold, "step0/grad", n, gsum[n] * np.float32(0.5))
+
+
+def test_sgd_restatements_bit_exact_vs_torch_optim():
+    """lenet_sgd_momentum must round exactly like torch.optim.SGD on CPU (3 steps)."""
+    g = torch.Generator().manual_seed(7)
+    p0 = torch.randn(10007, generator=g)
+    p_t = p0.clone().requires_grad_(True)
+    opt = torch.optim.SGD([p_t], lr=0.01, momentum=0.5)
+    p_c = p0.numpy().copy()
+    buf_c = np.zeros_like(p_c)
+    for step in range(3):
+        grad = torch.randn(10007, generator=g)
+        p_t.grad = grad.clone()
+        opt.step()
+        c_oracle.sgd_momentum_(p_c, grad.numpy(), buf_c, 0.01, 0.5, 1.0, step == 0)
+        assert np.array_equal(p_c, p_t.detach().numpy()), f"step {step}"
+
+
+def test_eval_matches_reference():
+    gold = load_golden("eval_b1000")
+    params = mo.init_params(1)
+    correct = 0
+    for i, seed in enumerate((4321, 4322)):
+        x, t = mo.synthetic_batch(1000, seed)
+        _, c, logp = mo.evaluate(params, x, t)
+        correct += c
+        if i == 0:
+            assert_close(logp.numpy(), gold["logp_batch0"], what="logp torch")
+            act = c_oracle.forward({k: v.numpy() for k, v in params.items()}, x.numpy()[:64])
+            assert_close(act["logp"], gold["logp_batch0"][:64], what="logp C")
+    assert correct / 2000.0 == float(gold["accuracy"][0])
+
+
+def test_smoke_sendrecv_bit_exact():
+    gold = load_golden("smoke_sendrecv_ws3")
+    torch.manual_seed(0)
+    inp = torch.randn(2, 2)
+    assert np.array_equal(inp.numpy(), gold["inp"])
+    for w, res in enumerate(mo.smoke_sendrecv(inp, 3), start=1):
+        assert np.array_equal(res.numpy(), gold[f"result_from_worker{w}"])
+        assert np.array_equal(c_oracle.square(inp.numpy()), gold[f"result_from_worker{w}"])
