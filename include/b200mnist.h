@@ -1,0 +1,148 @@
+/*
+ * b200mnist.h -- C ABI of libb200mnist.so: the examples/mnist training step and the
+ * examples/smoke-dist worker op as hand-written sm_100a CUDA kernels.
+ *
+ * The reference (jiaqianjing/pytorch-operator) has no native code: its payloads reach
+ * native kernels only through PyTorch.  Each entry point below therefore cites the
+ * line of the reference PAYLOAD whose library call it replaces
+ * (examples/mnist/mnist.py, examples/smoke-dist/dist_sendrecv.py under /root/reference).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; all tensors are
+ *     dense fp32 in the reference's layouts (NCHW activations, [out,in,kh,kw] conv
+ *     weights, [out,in] linear weights), targets are int64 as torch hands them over;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); every
+ *     call only enqueues work on it -- no allocation, no synchronisation, no retained
+ *     pointers -- so calls are legal inside CUDA-graph stream capture;
+ *   - return value: 0 on success, negative on failure (-cudaError_t for CUDA errors,
+ *     -10000-k for argument error k); b200mnist_last_error() gives the text of the last
+ *     failure on the calling thread.  Nothing throws across this boundary;
+ *   - the caller owns all memory.  Workspaces are caller-allocated, sized by
+ *     b200mnist_workspace_bytes(), 256-byte aligned, and must be zero-filled ONCE before
+ *     their first use (they hold self-resetting counters);
+ *   - one host thread per device context at a time (the reference runs one Python
+ *     thread per process/pod).
+ */
+#ifndef B200MNIST_H
+#define B200MNIST_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- flat parameter bucket ------------------------------------------------------
+ * The eight tensors of Net (mnist.py:17-23) live in ONE flat fp32 buffer so that
+ * the DDP gradient exchange (mnist.py:135-138) is a single collective and the SGD
+ * update (mnist.py:140,43) a single kernel.  Each tensor starts on a 256-byte
+ * boundary; pad elements stay zero.  Index: 0 conv1.weight 1 conv1.bias 2 conv2.weight
+ * 3 conv2.bias 4 fc1.weight 5 fc1.bias 6 fc2.weight 7 fc2.bias. */
+#define B200MNIST_NUM_TENSORS 8
+#define B200MNIST_PARAM_ELEMS 431080 /* real parameters */
+#define B200MNIST_FLAT_ELEMS 431296  /* with alignment padding */
+int64_t b200mnist_flat_elems(void);
+int64_t b200mnist_tensor_offset(int index); /* element offset in the flat buffer, -1 if bad index */
+int64_t b200mnist_tensor_elems(int index);  /* element count, -1 if bad index */
+
+const char *b200mnist_last_error(void);
+int b200mnist_version(void);
+
+/* Bytes of workspace the step entry points need for batches up to `max_batch`. */
+int64_t b200mnist_workspace_bytes(int max_batch);
+
+/* ---- whole-step entry points ----------------------------------------------------- */
+
+/* Replaces, for one batch, mnist.py:39-42: zero_grad(); output = model(data);
+ * loss = F.nll_loss(output, target); loss.backward().
+ *   params, grads : flat buckets (B200MNIST_FLAT_ELEMS floats); grads is overwritten
+ *   x [B,1,28,28], target int64[B]
+ *   loss_out : 1 float, the mean NLL of this batch
+ *   logp_out : optional [B,10] log-probabilities (may be NULL)
+ * An out-of-range target makes loss_out NaN (torch raises there). */
+int b200mnist_forward_backward(const float *params, float *grads, const float *x, const int64_t *target, int B,
+                               void *workspace, int64_t workspace_bytes, float *loss_out, float *logp_out,
+                               void *stream);
+
+/* Same as b200mnist_forward_backward followed by b200mnist_sgd_momentum in one call,
+ * with the gradient reduction fused into the update (single-process training,
+ * mnist.py:39-43 when WORLD_SIZE == 1). */
+int b200mnist_train_step(float *params, float *grads, float *momentum, const float *x, const int64_t *target, int B,
+                         void *workspace, int64_t workspace_bytes, float lr, float mu, int first_step,
+                         float *loss_out, void *stream);
+
+/* Replaces model(data) under torch.no_grad() plus the per-batch reductions of test(),
+ * mnist.py:56-61: logp_out [B,10] (may be NULL); stats_out[0] = sum of NLL
+ * (F.nll_loss(reduction='sum')), stats_out[1] = number of rows whose argmax equals target. */
+int b200mnist_forward_eval(const float *params, const float *x, const int64_t *target, int B, void *workspace,
+                           int64_t workspace_bytes, float *logp_out, float *stats_out, void *stream);
+
+/* Replaces optimizer.step() of optim.SGD(lr, momentum) (mnist.py:140,43) fused with the
+ * 1/world_size of DDP's gradient averaging (mnist.py:135-138) as grad_scale:
+ *   g = grads*grad_scale; buf = first_step ? g : mu*buf + g; p = p - lr*buf
+ * over n contiguous floats, rounded exactly like the ATen CPU kernels (bit-exact). */
+int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, int64_t n, float lr, float mu,
+                           float grad_scale, int first_step, void *stream);
+
+/* ---- per-layer entry points (used by the autograd bridge and the unit tests) ------- */
+
+/* F.max_pool2d(F.relu(conv1(x)), 2, 2), mnist.py:26-27.  x [B,1,28,28], w [20,1,5,5],
+ * out [B,20,12,12]; idx [B,20,12,12] uint8 = slot (dy*2+dx) of the window maximum. */
+int b200mnist_conv1_relu_pool_fwd(const float *x, const float *w, const float *bias, float *out, uint8_t *idx,
+                                  int B, void *stream);
+/* F.max_pool2d(F.relu(conv2(x)), 2, 2), mnist.py:28-29.  in [B,20,12,12], w [50,20,5,5],
+ * out [B,50,4,4] (= the [B,800] view of mnist.py:30). */
+int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
+                                  int B, void *stream);
+/* F.relu(fc1(x)), mnist.py:31.  in [B,800], w [500,800], out [B,500].  `scratch` must hold
+ * b200mnist_fc1_scratch_bytes(B) bytes (split-K partial sums). */
+int64_t b200mnist_fc1_scratch_bytes(int B);
+int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, float *out, int B, void *scratch,
+                           void *stream);
+/* F.log_softmax(fc2(h), dim=1) and F.nll_loss (mean), mnist.py:32-33,41, plus the start of
+ * loss.backward() (mnist.py:42): dz2 = (softmax - onehot)/B and dz1 = (dz2 . W2) * (h > 0).
+ * h [B,500]; logp [B,10]; dz2 [B,10]; dz1 [B,500] (NULL to skip the backward part);
+ * loss_out 1 float; scratch: (B + 64) floats, zero-filled once. */
+int b200mnist_fc2_logsoftmax_nll(const float *h, const float *w, const float *bias, const int64_t *target, int B,
+                                 float *logp, float *loss_out, float *dz2, float *dz1, void *scratch,
+                                 void *stream);
+/* Backward of log_softmax + fc2 for an arbitrary upstream gradient (autograd of mnist.py:32-33
+ * when the loss is not the fused NLL): dz2 = dlogp - exp(logp)*sum_j(dlogp), dz1 = (dz2 . W2)*(h>0). */
+int b200mnist_head_bwd(const float *logp, const float *dlogp, const float *h, const float *w, int B, float *dz2,
+                       float *dz1, void *stream);
+/* Backward of the two linear layers, mnist.py:42: gW2 [10,500], gb2 [10], gW1 [500,800],
+ * gb1 [500], dp2 [B,800] = dz1 . W1.  scratch: b200mnist_fc_bwd_scratch_bytes(B). */
+int64_t b200mnist_fc_bwd_scratch_bytes(int B);
+int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
+                     float *gw2, float *gb2, float *gw1, float *gb1, float *dp2, void *scratch, void *stream);
+/* Backward of conv2+ReLU+pool, mnist.py:42: given dp2 [B,50,4,4] (gradient of the pooled
+ * output), the saved p2/idx2/p1 and conv2.weight, writes gw [50,20,5,5], gb [50] and
+ * dp1 [B,20,12,12].  scratch: b200mnist_conv2_bwd_scratch_bytes(B). */
+int64_t b200mnist_conv2_bwd_scratch_bytes(int B);
+int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, const float *p1, const float *w,
+                        int B, float *gw, float *gb, float *dp1, void *scratch, void *stream);
+/* Backward of conv1+ReLU+pool, mnist.py:42 (weights only: the input needs no gradient).
+ * gw [20,1,5,5], gb [20].  scratch: b200mnist_conv1_bwd_scratch_bytes(B). */
+int64_t b200mnist_conv1_bwd_scratch_bytes(int B);
+int b200mnist_conv1_bwd(const float *dp1, const float *p1, const uint8_t *idx1, const float *x, int B, float *gw,
+                        float *gb, void *scratch, void *stream);
+
+/* The worker's op in examples/smoke-dist/dist_sendrecv.py:32, torch.mul(inp, inp). */
+int b200mnist_square(const float *in, float *out, int64_t n, void *stream);
+
+/* ---- instrumentation for bench.py (no counterpart in the reference) ----------------
+ * b200mnist_launch_count: kernels this library has launched in this process so far.
+ * b200mnist_profile_begin/end: while enabled, a CUDA event is recorded on `stream` after
+ * every kernel the library launches; _end synchronises the stream and returns the number n
+ * of kernels seen, their durations (ms, event to event) and their names (static strings)
+ * in the HOST arrays.  delay_us > 0 first parks the stream for that long so the following
+ * launches queue up (no host launch gaps inside the timings).  Not for use under capture. */
+long long b200mnist_launch_count(void);
+int b200mnist_profile_begin(void *stream, int delay_us);
+int b200mnist_profile_end(float *ms_out_host, const char **names_out_host, int cap, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MNIST_H */

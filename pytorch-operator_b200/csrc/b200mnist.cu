@@ -1,0 +1,499 @@
+// libb200mnist.so -- C ABI over the sm_100a kernels (declared in include/b200mnist.h).
+// Host code here only validates arguments, carves the caller's workspace and enqueues
+// kernels on the caller's stream: no allocation, no synchronisation, no retained state.
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/b200mnist.h"
+#include "common.cuh"
+#include "conv_bwd.cuh"
+#include "conv_fwd.cuh"
+#include "fc.cuh"
+#include "optim.cuh"
+
+using namespace b200mnist;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail_arg(int code, const char *msg) {
+    g_last_error = msg;
+    return -10000 - code;
+}
+int fail_cuda(cudaError_t e, const char *where) {
+    g_last_error = std::string(where) + ": " + cudaGetErrorString(e);
+    return -(int)e;
+}
+// ---- instrumentation: launch counter + optional per-kernel CUDA-event timing ----
+constexpr int kProfMax = 64;
+struct Profiler {
+    bool enabled = false;
+    int count = 0;
+    cudaEvent_t ev[kProfMax + 1] = {};
+    bool created = false;
+    const char *names[kProfMax] = {};
+};
+Profiler g_prof;
+long long g_launches = 0;
+
+inline void note_launch(const char *where, cudaStream_t s) {
+    ++g_launches;
+    if (g_prof.enabled && g_prof.count < kProfMax) {
+        g_prof.names[g_prof.count] = where;
+        cudaEventRecord(g_prof.ev[++g_prof.count], s);
+    }
+}
+#define CHECK_LAUNCH(where, stream)                           \
+    do {                                                      \
+        cudaError_t e_ = cudaGetLastError();                  \
+        if (e_ != cudaSuccess) return fail_cuda(e_, where);   \
+        note_launch(where, stream);                           \
+    } while (0)
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- how each batch-dependent kernel is split (a pure function of B) ----
+struct Plan {
+    int fc1_split, fc1_kchunk;  // fc1 forward split-K
+    int dg_split, dg_kchunk;    // fc1 data-gradient split-K
+    int fc2w_split, fc2w_rows;  // fc2 weight-gradient batch split
+    int c2w_split;              // conv2 weight-gradient batch split
+    int c1w_split;              // conv1 weight-gradient batch split
+    int c2dg_gx;                // conv2 data-gradient CTAs per channel tile
+};
+Plan make_plan(int B) {
+    Plan p;
+    const int gy = ceil_div(B, 64);
+    p.fc1_split = clampi(ceil_div(200, 16 * gy), 1, 10);
+    p.fc1_kchunk = ceil_div(ceil_div(800, p.fc1_split), kGemmBK) * kGemmBK;
+    p.fc1_split = ceil_div(800, p.fc1_kchunk);
+    p.dg_split = clampi(ceil_div(200, 25 * gy), 1, 8);
+    p.dg_kchunk = ceil_div(ceil_div(500, p.dg_split), kGemmBK) * kGemmBK;
+    p.dg_split = ceil_div(500, p.dg_kchunk);
+    p.fc2w_split = clampi(ceil_div(B, 16), 1, 32);
+    p.fc2w_rows = ceil_div(B, p.fc2w_split);
+    p.fc2w_split = ceil_div(B, p.fc2w_rows);
+    p.c2w_split = clampi(ceil_div(B, 2), 1, 29);
+    p.c1w_split = clampi(B, 1, 148);
+    p.c2dg_gx = clampi(B, 1, 88);
+    return p;
+}
+
+// ---- workspace carving (all regions 256-byte aligned) ----
+struct Workspace {
+    unsigned *ticket;
+    float *stats;  // [0] loss / nll sum, [1] correct
+    float *p1, *p2, *h, *logp, *dz2, *dz1, *dp1, *rows;
+    uint8_t *i1, *i2;
+    float *fc1_part, *dp2_part, *fc2w_part, *c2w_part, *c1w_part;
+    size_t bytes;
+};
+Workspace carve(void *base, int B) {
+    // Partial-sum regions are sized for the worst split of any batch <= B.
+    Workspace w;
+    size_t off = 0;
+    auto take = [&](size_t nbytes) {
+        void *p = base ? static_cast<char *>(base) + off : nullptr;
+        off += align256(nbytes);
+        return p;
+    };
+    const size_t Bz = (size_t)B;
+    w.ticket = static_cast<unsigned *>(take(256));
+    w.stats = static_cast<float *>(take(256));
+    w.p1 = static_cast<float *>(take(Bz * kP1Elems * 4));
+    w.i1 = static_cast<uint8_t *>(take(Bz * kP1Elems));
+    w.p2 = static_cast<float *>(take(Bz * kP2Elems * 4));
+    w.i2 = static_cast<uint8_t *>(take(Bz * kP2Elems));
+    w.h = static_cast<float *>(take(Bz * kHElems * 4));
+    w.logp = static_cast<float *>(take(Bz * kClasses * 4));
+    w.dz2 = static_cast<float *>(take(Bz * kClasses * 4));
+    w.dz1 = static_cast<float *>(take(Bz * kHElems * 4));
+    w.dp1 = static_cast<float *>(take(Bz * kP1Elems * 4));
+    w.rows = static_cast<float *>(take(Bz * 2 * 4));
+    w.fc1_part = static_cast<float *>(take(10 * Bz * 512 * 4));
+    w.dp2_part = static_cast<float *>(take(8 * Bz * kP2Elems * 4));
+    w.fc2w_part = static_cast<float *>(take((size_t)32 * kFc2PartStride * 4));
+    w.c2w_part = static_cast<float *>(take((size_t)29 * kC2PartStride * 4));
+    w.c1w_part = static_cast<float *>(take((size_t)148 * kC1PartStride * 4));
+    w.bytes = off;
+    return w;
+}
+
+int check_step_args(const void *params, const void *x, const void *target, int B, void *workspace,
+                    int64_t workspace_bytes) {
+    if (!params || !x || !target || !workspace) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(params) || !aligned16(x) || (reinterpret_cast<uintptr_t>(workspace) & 255u))
+        return fail_arg(3, "params/x must be 16-byte aligned and workspace 256-byte aligned");
+    if ((int64_t)carve(nullptr, B).bytes > workspace_bytes) return fail_arg(4, "workspace too small for this batch");
+    return 0;
+}
+
+// ---- launches of the individual stages ----
+int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out, uint8_t *idx, int B, cudaStream_t s) {
+    conv1_relu_pool_fwd_kernel<<<dim3(B, 20 / kC1ChPerCta), kC1Threads, 0, s>>>(x, w, b, out, idx, B);
+    CHECK_LAUNCH("conv1_relu_pool_fwd", s);
+    return 0;
+}
+int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
+                     cudaStream_t s) {
+    conv2_relu_pool_fwd_kernel<<<dim3(ceil_div(B, kC2ImgPerCta), 50 / kC2OcPerCta), kC2Threads, 0, s>>>(in, w, b, out,
+                                                                                                      idx, B);
+    CHECK_LAUNCH("conv2_relu_pool_fwd", s);
+    return 0;
+}
+// fc1 forward: returns the number of split-K partials left in `part` (0 = `h` is final).
+int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h, float *part, int B, const Plan &pl,
+                   cudaStream_t s, int *nsplit_out) {
+    GemmArgs g{};
+    g.A = in; g.B = w; g.M = B; g.N = 500; g.K = 800; g.lda = 800; g.ldb = 800; g.kchunk = pl.fc1_kchunk;
+    if (pl.fc1_split == 1) {
+        g.C = h; g.ldc = 500; g.bias = bias; g.relu = 1;
+    } else {
+        g.C = part; g.ldc = 512;
+    }
+    gemm_kernel<64, 32, 4, 2, true, true><<<dim3(ceil_div(500, 32), ceil_div(B, 64), pl.fc1_split), 256, 0, s>>>(g);
+    CHECK_LAUNCH("fc1 forward gemm", s);
+    *nsplit_out = pl.fc1_split == 1 ? 0 : pl.fc1_split;
+    return 0;
+}
+int launch_head(const HeadArgs &a, cudaStream_t s) {
+    head_kernel<<<a.B, kHeadThreads, 0, s>>>(a);
+    CHECK_LAUNCH("fc2/log_softmax/nll head", s);
+    return 0;
+}
+int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
+                  float *gw1, float *gb1, float *dp2_part, float *fc2w_part, const Plan &pl, cudaStream_t s) {
+    fc2_wgrad_kernel<<<dim3(ceil_div(500, kFc2wThreads), pl.fc2w_split), kFc2wThreads, 0, s>>>(dz2, h, fc2w_part, B,
+                                                                                               pl.fc2w_rows);
+    CHECK_LAUNCH("fc2 wgrad", s);
+    GemmArgs g{};  // gW1[n,k] = sum_b dz1[b,n] p2[b,k] ; gb1[n] = sum_b dz1[b,n]
+    g.A = dz1; g.B = p2; g.C = gw1; g.rowsum = gb1;
+    g.M = 500; g.N = 800; g.K = B; g.lda = 500; g.ldb = 800; g.ldc = 800; g.kchunk = B;
+    gemm_kernel<64, 64, 4, 4, false, false><<<dim3(ceil_div(800, 64), ceil_div(500, 64), 1), 256, 0, s>>>(g);
+    CHECK_LAUNCH("fc1 wgrad gemm", s);
+    GemmArgs d{};  // dp2[b,k] = sum_n dz1[b,n] W1[n,k]
+    d.A = dz1; d.B = w1; d.C = dp2_part;
+    d.M = B; d.N = 800; d.K = 500; d.lda = 500; d.ldb = 800; d.ldc = 800; d.kchunk = pl.dg_kchunk;
+    gemm_kernel<64, 32, 4, 2, true, false><<<dim3(ceil_div(800, 32), ceil_div(B, 64), pl.dg_split), 256, 0, s>>>(d);
+    CHECK_LAUNCH("fc1 dgrad gemm", s);
+    return 0;
+}
+int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const float *p2, const uint8_t *i2,
+                     const float *p1, const float *w, int B, float *dp1, float *c2w_part, const Plan &pl,
+                     cudaStream_t s) {
+    static bool attr_done = false;  // per process; setting it again is harmless
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             kDgSmemBytes);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(conv2_dgrad)");
+        attr_done = true;
+    }
+    conv2_dgrad_kernel<<<dim3(pl.c2dg_gx, 20 / kDgIcPerCta), kDgThreads, kDgSmemBytes, s>>>(dp2, nsplit, split_stride,
+                                                                                            p2, i2, w, dp1, B);
+    CHECK_LAUNCH("conv2 dgrad", s);
+    conv2_wgrad_kernel<<<dim3(20 / kWgIcPerCta, pl.c2w_split), kWgThreads, 0, s>>>(dp2, nsplit, split_stride, p2, i2,
+                                                                                   p1, c2w_part, B);
+    CHECK_LAUNCH("conv2 wgrad", s);
+    return 0;
+}
+int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
+                     const Plan &pl, cudaStream_t s) {
+    conv1_wgrad_kernel<<<pl.c1w_split, kC1wThreads, 0, s>>>(x, dp1, p1, i1, c1w_part, B);
+    CHECK_LAUNCH("conv1 wgrad", s);
+    return 0;
+}
+
+GradSegment seg(int off, int n, const float *part, int nsplit, int stride) {
+    GradSegment g;
+    g.off = off; g.n = n; g.part = part; g.nsplit = nsplit; g.stride = stride;
+    return g;
+}
+GradSegments step_segments(const Workspace &w, const Plan &pl) {
+    GradSegments s{};
+    s.seg[0] = seg(kOffC1W, 500, w.c1w_part, pl.c1w_split, kC1PartStride);
+    s.seg[1] = seg(kOffC1B, 20, w.c1w_part + 512, pl.c1w_split, kC1PartStride);
+    s.seg[2] = seg(kOffC2W, 25000, w.c2w_part, pl.c2w_split, kC2PartStride);
+    s.seg[3] = seg(kOffC2B, 50, w.c2w_part + 25024, pl.c2w_split, kC2PartStride);
+    s.seg[4] = seg(kOffF2W, 5000, w.fc2w_part, pl.fc2w_split, kFc2PartStride);
+    s.seg[5] = seg(kOffF2B, 10, w.fc2w_part + 5056, pl.fc2w_split, kFc2PartStride);
+    s.count = 6;
+    return s;
+}
+int launch_finalize(float *grads, const GradSegments &segs, cudaStream_t s) {
+    const int n = kFlatElems - (kOffF2W - kOffF1W);
+    grad_finalize_kernel<<<ceil_div(n, 256), 256, 0, s>>>(grads, segs);
+    CHECK_LAUNCH("grad finalize", s);
+    return 0;
+}
+// out[i] = sum of the partials (used by the per-layer entry points)
+int reduce_to(float *out, int n, const float *part, int nsplit, int stride, cudaStream_t s) {
+    reduce_partials_to_kernel<<<ceil_div(n, 256), 256, 0, s>>>(out, part, n, nsplit, stride);
+    CHECK_LAUNCH("partial reduce", s);
+    return 0;
+}
+int launch_sgd(float *p, float *g, float *m, int64_t n, float lr, float mu, float scale, int first,
+               const GradSegments *segs, cudaStream_t s) {
+    const int blocks = (int)((n + 1023) / 1024);
+    if (segs) {
+        sgd_momentum_kernel<true><<<blocks, 256, 0, s>>>(p, g, m, (int)n, -lr, mu, scale, first, *segs);
+    } else {
+        GradSegments none{};
+        sgd_momentum_kernel<false><<<blocks, 256, 0, s>>>(p, g, m, (int)n, -lr, mu, scale, first, none);
+    }
+    CHECK_LAUNCH("sgd momentum", s);
+    return 0;
+}
+
+// forward (+ optional backward up to the partial gradients)
+int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target, int B, const Workspace &w,
+                const Plan &pl, bool backward, float *logp_out, float *stats_out, float loss_scale, int want_correct,
+                cudaStream_t s) {
+    int rc;
+    if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s))) return rc;
+    if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, s))) return rc;
+    int nsplit = 0;
+    if ((rc = launch_fc1_fwd(w.p2, P + kOffF1W, P + kOffF1B, w.h, w.fc1_part, B, pl, s, &nsplit))) return rc;
+    HeadArgs a{};
+    a.h_in = w.h; a.part = w.fc1_part; a.b1 = P + kOffF1B; a.h_out = w.h;
+    a.w2 = P + kOffF2W; a.b2 = P + kOffF2B; a.target = target;
+    a.logp = logp_out ? logp_out : w.logp;
+    a.dz2 = backward ? w.dz2 : nullptr; a.dz1 = backward ? w.dz1 : nullptr;
+    a.rows = w.rows; a.ticket = w.ticket; a.stats_out = stats_out;
+    a.B = B; a.nsplit = nsplit; a.want_correct = want_correct; a.inv_B = 1.0f / (float)B; a.loss_scale = loss_scale;
+    if ((rc = launch_head(a, s))) return rc;
+    if (!backward) return 0;
+    if ((rc = launch_fc_bwd(w.dz2, w.dz1, w.h, w.p2, P + kOffF1W, B, G + kOffF1W, G + kOffF1B, w.dp2_part,
+                            w.fc2w_part, pl, s)))
+        return rc;
+    if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B, w.dp1,
+                               w.c2w_part, pl, s)))
+        return rc;
+    return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t b200mnist_flat_elems(void) { return kFlatElems; }
+int64_t b200mnist_tensor_offset(int i) { return (i < 0 || i >= kNumTensors) ? -1 : kTensorOff[i]; }
+int64_t b200mnist_tensor_elems(int i) { return (i < 0 || i >= kNumTensors) ? -1 : kTensorElems[i]; }
+const char *b200mnist_last_error(void) { return g_last_error.c_str(); }
+int b200mnist_version(void) { return 100; }
+
+int64_t b200mnist_workspace_bytes(int max_batch) {
+    if (max_batch < 1 || max_batch > 65536) return -1;
+    return (int64_t)carve(nullptr, max_batch).bytes;
+}
+
+int b200mnist_forward_backward(const float *params, float *grads, const float *x, const int64_t *target, int B,
+                               void *workspace, int64_t workspace_bytes, float *loss_out, float *logp_out,
+                               void *stream) {
+    int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
+    if (rc) return rc;
+    if (!grads || !loss_out || !aligned16(grads)) return fail_arg(5, "grads/loss_out null or grads unaligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const Plan pl = make_plan(B);
+    const Workspace w = carve(workspace, B);
+    if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, logp_out, loss_out, 1.0f / (float)B, 0, s)))
+        return rc;
+    return launch_finalize(grads, step_segments(w, pl), s);
+}
+
+int b200mnist_train_step(float *params, float *grads, float *momentum, const float *x, const int64_t *target, int B,
+                         void *workspace, int64_t workspace_bytes, float lr, float mu, int first_step,
+                         float *loss_out, void *stream) {
+    int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
+    if (rc) return rc;
+    if (!grads || !momentum || !loss_out || !aligned16(grads) || !aligned16(momentum))
+        return fail_arg(5, "grads/momentum/loss_out null or unaligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const Plan pl = make_plan(B);
+    const Workspace w = carve(workspace, B);
+    if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s)))
+        return rc;
+    const GradSegments segs = step_segments(w, pl);
+    return launch_sgd(params, grads, momentum, kFlatElems, lr, mu, 1.0f, first_step, &segs, s);
+}
+
+int b200mnist_forward_eval(const float *params, const float *x, const int64_t *target, int B, void *workspace,
+                           int64_t workspace_bytes, float *logp_out, float *stats_out, void *stream) {
+    int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
+    if (rc) return rc;
+    if (!stats_out) return fail_arg(5, "stats_out is null");
+    const Plan pl = make_plan(B);
+    const Workspace w = carve(workspace, B);
+    return run_fwd_bwd(params, nullptr, x, target, B, w, pl, false, logp_out, stats_out, 1.0f, 1,
+                       static_cast<cudaStream_t>(stream));
+}
+
+int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, int64_t n, float lr, float mu,
+                           float grad_scale, int first_step, void *stream) {
+    if (!params || !grads || !momentum) return fail_arg(1, "null pointer argument");
+    if (n < 0 || n > (int64_t)1 << 30) return fail_arg(2, "n out of range");
+    if (n == 0) return 0;
+    if (!aligned16(params) || !aligned16(grads) || !aligned16(momentum))
+        return fail_arg(3, "params/grads/momentum must be 16-byte aligned");
+    return launch_sgd(params, const_cast<float *>(grads), momentum, n, lr, mu, grad_scale, first_step, nullptr,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int b200mnist_conv1_relu_pool_fwd(const float *x, const float *w, const float *bias, float *out, uint8_t *idx, int B,
+                                  void *stream) {
+    if (!x || !w || !bias || !out || !idx) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(x)) return fail_arg(3, "x must be 16-byte aligned");
+    return launch_conv1_fwd(x, w, bias, out, idx, B, static_cast<cudaStream_t>(stream));
+}
+
+int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *bias, float *out, uint8_t *idx, int B,
+                                  void *stream) {
+    if (!in || !w || !bias || !out || !idx) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(in)) return fail_arg(3, "in must be 16-byte aligned");
+    return launch_conv2_fwd(in, w, bias, out, idx, B, static_cast<cudaStream_t>(stream));
+}
+
+int64_t b200mnist_fc1_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)10 * B * 512 * 4; }
+
+int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, float *out, int B, void *scratch,
+                           void *stream) {
+    if (!in || !w || !bias || !out || !scratch) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(in) || !aligned16(w) || !aligned16(scratch)) return fail_arg(3, "in/w/scratch must be 16-byte aligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Plan pl = make_plan(B);
+    pl.fc1_split = 1;  // standalone call: finish in the GEMM epilogue, `scratch` stays unused
+    pl.fc1_kchunk = 800;
+    int nsplit = 0;
+    return launch_fc1_fwd(in, w, bias, out, static_cast<float *>(scratch), B, pl, s, &nsplit);
+}
+
+int b200mnist_fc2_logsoftmax_nll(const float *h, const float *w, const float *bias, const int64_t *target, int B,
+                                 float *logp, float *loss_out, float *dz2, float *dz1, void *scratch, void *stream) {
+    if (!h || !w || !bias || !target || !loss_out || !scratch) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    HeadArgs a{};
+    a.h_in = h; a.w2 = w; a.b2 = bias; a.target = target; a.logp = logp; a.dz2 = dz2; a.dz1 = dz1;
+    a.ticket = static_cast<unsigned *>(scratch);
+    a.rows = static_cast<float *>(scratch) + 64;
+    a.stats_out = loss_out;
+    a.B = B; a.nsplit = 0; a.want_correct = 0; a.inv_B = 1.0f / (float)B; a.loss_scale = 1.0f / (float)B;
+    return launch_head(a, static_cast<cudaStream_t>(stream));
+}
+
+int b200mnist_head_bwd(const float *logp, const float *dlogp, const float *h, const float *w, int B, float *dz2,
+                       float *dz1, void *stream) {
+    if (!logp || !dlogp || !h || !w || !dz2 || !dz1) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    head_bwd_kernel<<<B, kHeadThreads, 0, s>>>(logp, dlogp, h, w, dz2, dz1);
+    CHECK_LAUNCH("head backward", s);
+    return 0;
+}
+
+int64_t b200mnist_fc_bwd_scratch_bytes(int B) {
+    if (B < 1) return -1;
+    return (int64_t)align256((size_t)8 * B * kP2Elems * 4) + (int64_t)32 * kFc2PartStride * 4;
+}
+
+int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
+                     float *gw2, float *gb2, float *gw1, float *gb1, float *dp2, void *scratch, void *stream) {
+    if (!dz2 || !dz1 || !h || !p2 || !w1 || !gw2 || !gb2 || !gw1 || !gb1 || !dp2 || !scratch)
+        return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(dz1) || !aligned16(p2) || !aligned16(w1) || !aligned16(scratch))
+        return fail_arg(3, "dz1/p2/w1/scratch must be 16-byte aligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Plan pl = make_plan(B);
+    pl.dg_split = 1;  // standalone call: dp2 is written whole
+    pl.dg_kchunk = 512;
+    float *fc2w_part = reinterpret_cast<float *>(static_cast<char *>(scratch) + align256((size_t)8 * B * kP2Elems * 4));
+    int rc = launch_fc_bwd(dz2, dz1, h, p2, w1, B, gw1, gb1, dp2, fc2w_part, pl, s);
+    if (rc) return rc;
+    if ((rc = reduce_to(gw2, 5000, fc2w_part, pl.fc2w_split, kFc2PartStride, s))) return rc;
+    return reduce_to(gb2, 10, fc2w_part + 5056, pl.fc2w_split, kFc2PartStride, s);
+}
+
+int64_t b200mnist_conv2_bwd_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)29 * kC2PartStride * 4; }
+
+int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, const float *p1, const float *w, int B,
+                        float *gw, float *gb, float *dp1, void *scratch, void *stream) {
+    if (!dp2 || !p2 || !idx2 || !p1 || !w || !gw || !gb || !dp1 || !scratch) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(p1) || !aligned16(w) || !aligned16(scratch)) return fail_arg(3, "p1/w/scratch must be 16-byte aligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const Plan pl = make_plan(B);
+    float *part = static_cast<float *>(scratch);
+    int rc = launch_conv2_bwd(dp2, 1, 0, p2, idx2, p1, w, B, dp1, part, pl, s);
+    if (rc) return rc;
+    return reduce_to(gw, 25000, part, pl.c2w_split, kC2PartStride, s) ||
+           reduce_to(gb, 50, part + 25024, pl.c2w_split, kC2PartStride, s);
+}
+
+int64_t b200mnist_conv1_bwd_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)148 * kC1PartStride * 4; }
+
+int b200mnist_conv1_bwd(const float *dp1, const float *p1, const uint8_t *idx1, const float *x, int B, float *gw,
+                        float *gb, void *scratch, void *stream) {
+    if (!dp1 || !p1 || !idx1 || !x || !gw || !gb || !scratch) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(x)) return fail_arg(3, "x must be 16-byte aligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const Plan pl = make_plan(B);
+    float *part = static_cast<float *>(scratch);
+    int rc = launch_conv1_bwd(dp1, p1, idx1, x, B, part, pl, s);
+    if (rc) return rc;
+    return reduce_to(gw, 500, part, pl.c1w_split, kC1PartStride, s) ||
+           reduce_to(gb, 20, part + 512, pl.c1w_split, kC1PartStride, s);
+}
+
+int b200mnist_square(const float *in, float *out, int64_t n, void *stream) {
+    if (n < 0) return fail_arg(2, "n out of range");
+    if (n == 0) return 0;
+    if (!in || !out) return fail_arg(1, "null pointer argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    square_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, out, (long long)n);
+    CHECK_LAUNCH("square", s);
+    return 0;
+}
+
+/* ---- instrumentation (no counterpart in the reference) ---- */
+long long b200mnist_launch_count(void) { return g_launches; }
+
+int b200mnist_profile_begin(void *stream, int delay_us) {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (delay_us > 0) delay_kernel<<<1, 1, 0, s>>>((unsigned long long)delay_us * 1000ull);
+    if (!g_prof.created) {
+        for (int i = 0; i <= kProfMax; ++i) {
+            cudaError_t e = cudaEventCreate(&g_prof.ev[i]);
+            if (e != cudaSuccess) return fail_cuda(e, "cudaEventCreate");
+        }
+        g_prof.created = true;
+    }
+    g_prof.count = 0;
+    g_prof.enabled = true;
+    cudaError_t e = cudaEventRecord(g_prof.ev[0], s);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaEventRecord");
+    return 0;
+}
+
+int b200mnist_profile_end(float *ms_out_host, const char **names_out_host, int cap, void *stream) {
+    g_prof.enabled = false;
+    cudaError_t e = cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail_cuda(e, "cudaStreamSynchronize");
+    int n = g_prof.count < cap ? g_prof.count : cap;
+    for (int i = 0; i < n; ++i) {
+        e = cudaEventElapsedTime(&ms_out_host[i], g_prof.ev[i], g_prof.ev[i + 1]);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaEventElapsedTime");
+        names_out_host[i] = g_prof.names[i];
+    }
+    return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,269 @@
+// Backward kernels of the two conv + ReLU + max-pool stages (autograd of mnist.py:26-29,
+// run by loss.backward() at mnist.py:42).
+#pragma once
+#include "common.cuh"
+
+namespace b200mnist {
+
+// Gradient w.r.t. the conv2 output map of one image, built in shared memory from the
+// gradient of the pooled map: max-pool backward routes each value to the arg-max slot of
+// its 2x2 window, ReLU backward kills it where the (post-ReLU) maximum was 0.
+//   D_s : [50][ld] floats, already zero-filled; dp2 may be the sum of `nsplit` partials.
+__device__ __forceinline__ void scatter_dconv2(float *D_s, int ld, const float *__restrict__ dp2, int nsplit,
+                                               size_t split_stride, const float *__restrict__ p2,
+                                               const uint8_t *__restrict__ i2, size_t b, int tid, int nthreads) {
+    for (int e = tid; e < kP2Elems; e += nthreads) {
+        const size_t o = b * kP2Elems + e;
+        float g = dp2[o];
+        for (int s = 1; s < nsplit; ++s) g += dp2[s * split_stride + o];
+        if (p2[o] > 0.f) {
+            const int oc = e >> 4, p = e & 15, q = i2[o];
+            const int oy = 2 * (p >> 2) + (q >> 1), ox = 2 * (p & 3) + (q & 1);
+            D_s[oc * ld + oy * 8 + ox] = g;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------
+// conv2 data gradient as GEMM + col2im, per image and per tile of 4 input channels:
+//   T[(ic,ky,kx), (oy,ox)] = sum_oc W[oc,(ic,ky,kx)] * dconv2[oc,(oy,ox)]    (100 x 64, K = 50)
+//   dp1[ic,y,x]            = sum_{ky,kx} T[(ic,ky,kx), (y-ky, x-kx)]           (valid terms only)
+// This does the 1.6 M MAC/image a scatter formulation needs (a gather "full correlation"
+// over the zero-padded map would do 3.6 M), with all accumulation in registers and a
+// fixed summation order.  The weight tile is loaded once per CTA and reused across the
+// images the CTA loops over.
+// ---------------------------------------------------------------------------------
+constexpr int kDgIcPerCta = 4;
+constexpr int kDgThreads = 256;
+constexpr int kDgLdT = 68;
+constexpr int kDgSmemBytes = (50 * 100 + 50 * 64 + 100 * kDgLdT) * 4;  // 60,000 B (dynamic)
+
+__global__ void __launch_bounds__(kDgThreads)
+conv2_dgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_stride, const float *__restrict__ p2,
+                   const uint8_t *__restrict__ i2, const float *__restrict__ w, float *__restrict__ dp1, int B) {
+    extern __shared__ __align__(16) float smem[];
+    float *W_s = smem;                // [50 oc][100 m]
+    float *D_s = W_s + 50 * 100;      // [50 oc][64 n]
+    float *T_s = D_s + 50 * 64;       // [100 m][68]
+    const int tid = threadIdx.x, ic0 = blockIdx.y * kDgIcPerCta;
+    for (int i = tid; i < 50 * 25; i += kDgThreads) {
+        const int oc = i / 25, m4 = (i % 25) * 4;
+        *reinterpret_cast<float4 *>(&W_s[oc * 100 + m4]) =
+            __ldg(reinterpret_cast<const float4 *>(w + (size_t)oc * 500 + ic0 * 25 + m4));
+    }
+    const int tm = tid >> 3, tn = tid & 7;  // tm < 25 active: rows 4*tm..+3; cols 4*tn..+3 and 32+4*tn..+3
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+        for (int i = tid; i < 50 * 64 / 4; i += kDgThreads)
+            reinterpret_cast<float4 *>(D_s)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();  // also orders W_s (first trip) and the previous trip's T_s readers
+        scatter_dconv2(D_s, 64, dp2, nsplit, split_stride, p2, i2, (size_t)b, tid, kDgThreads);
+        __syncthreads();
+        if (tm < 25) {
+            float acc[4][8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll 5
+            for (int oc = 0; oc < 50; ++oc) {
+                const float4 a = *reinterpret_cast<const float4 *>(&W_s[oc * 100 + tm * 4]);
+                const float4 b0 = *reinterpret_cast<const float4 *>(&D_s[oc * 64 + tn * 4]);
+                const float4 b1 = *reinterpret_cast<const float4 *>(&D_s[oc * 64 + 32 + tn * 4]);
+                const float av[4] = {a.x, a.y, a.z, a.w};
+                const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float *row = &T_s[(tm * 4 + i) * kDgLdT];
+                *reinterpret_cast<float4 *>(row + tn * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+                *reinterpret_cast<float4 *>(row + 32 + tn * 4) =
+                    make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+            }
+        }
+        __syncthreads();
+        for (int o = tid; o < kDgIcPerCta * 144; o += kDgThreads) {
+            const int icl = o / 144, r = o - icl * 144, y = r / 12, x = r - y * 12;
+            float s = 0.f;
+#pragma unroll
+            for (int ky = 0; ky < 5; ++ky) {
+                const int oy = y - ky;
+                if (oy < 0 || oy >= 8) continue;
+#pragma unroll
+                for (int kx = 0; kx < 5; ++kx) {
+                    const int ox = x - kx;
+                    if (ox < 0 || ox >= 8) continue;
+                    s += T_s[(icl * 25 + ky * 5 + kx) * kDgLdT + oy * 8 + ox];
+                }
+            }
+            dp1[(size_t)b * kP1Elems + (ic0 + icl) * 144 + r] = s;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------
+// conv2 weight/bias gradient, dense, register resident:
+//   gW[oc,ic,ky,kx] = sum_b sum_{oy,ox} dconv2[b,oc,oy,ox] * p1[b,ic,oy+ky,ox+kx]
+// CTA = tile of 4 input channels x a slice of the batch; 8 warps = 4 channels x 2 images in
+// flight; lane = output channel pair {lane, lane+25} (25 active lanes), so each thread keeps
+// 2x25 accumulators.  Per conv row it loads a 5x12 strip of p1 (warp-uniform broadcast) and
+// 2x8 gradient values (row stride 68 floats: conflict-free LDS.128) for 400 FMAs -- about 21
+// FMA per shared-memory load.  Each CTA writes its partial [25,056 + 64]; the partials of the
+// batch slices are summed in a fixed order by grad_finalize / the fused SGD kernel.
+// ---------------------------------------------------------------------------------
+constexpr int kWgIcPerCta = 4;
+constexpr int kWgThreads = 256;
+constexpr int kWgLdD = 68;
+constexpr int kC2PartStride = 25088;  // 25,000 weights @0, 50 biases @25,024
+
+__global__ void __launch_bounds__(kWgThreads)
+conv2_wgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_stride, const float *__restrict__ p2,
+                   const uint8_t *__restrict__ i2, const float *__restrict__ p1, float *__restrict__ part, int B) {
+    __shared__ __align__(16) float P_s[2][kWgIcPerCta * 144];  //  4,608 B
+    __shared__ __align__(16) float D_s[2][50 * kWgLdD];        // 27,200 B (later: the 50 x 100 output tile)
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, icl = warp & 3, par = warp >> 2;
+    const int ic0 = blockIdx.x * kWgIcPerCta;
+    const bool active = lane < 25;
+    float acc0[5][5], acc1[5][5], accb0 = 0.f, accb1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 5; ++i)
+#pragma unroll
+        for (int j = 0; j < 5; ++j) acc0[i][j] = acc1[i][j] = 0.f;
+
+    for (int bb = blockIdx.y * 2; bb < B; bb += gridDim.y * 2) {
+        __syncthreads();  // previous trip's readers are done
+        for (int i = tid; i < 2 * 50 * kWgLdD / 4; i += kWgThreads)
+            reinterpret_cast<float4 *>(&D_s[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = tid; i < 2 * kWgIcPerCta * 36; i += kWgThreads) {
+            const int pr = i / (kWgIcPerCta * 36), r = i - pr * (kWgIcPerCta * 36), b = bb + pr;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (b < B) v = __ldg(reinterpret_cast<const float4 *>(p1 + (size_t)b * kP1Elems + ic0 * 144) + r);
+            reinterpret_cast<float4 *>(&P_s[pr][0])[r] = v;
+        }
+        __syncthreads();
+        scatter_dconv2(&D_s[0][0], kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb, tid, kWgThreads);
+        if (bb + 1 < B)
+            scatter_dconv2(&D_s[1][0], kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb + 1, tid, kWgThreads);
+        __syncthreads();
+        if (active && bb + par < B) {
+            const float *ps = &P_s[par][icl * 144];
+            const float *d0p = &D_s[par][lane * kWgLdD];
+            const float *d1p = &D_s[par][(lane + 25) * kWgLdD];
+#pragma unroll 1
+            for (int oy = 0; oy < 8; ++oy) {
+                float strip[5][12];
+#pragma unroll
+                for (int r = 0; r < 5; ++r)
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        const float4 v = *reinterpret_cast<const float4 *>(ps + (oy + r) * 12 + 4 * j);
+                        strip[r][4 * j] = v.x; strip[r][4 * j + 1] = v.y;
+                        strip[r][4 * j + 2] = v.z; strip[r][4 * j + 3] = v.w;
+                    }
+                const float4 da = *reinterpret_cast<const float4 *>(d0p + oy * 8);
+                const float4 db = *reinterpret_cast<const float4 *>(d0p + oy * 8 + 4);
+                const float4 dc = *reinterpret_cast<const float4 *>(d1p + oy * 8);
+                const float4 dd = *reinterpret_cast<const float4 *>(d1p + oy * 8 + 4);
+                const float d0[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
+                const float d1[8] = {dc.x, dc.y, dc.z, dc.w, dd.x, dd.y, dd.z, dd.w};
+#pragma unroll
+                for (int ox = 0; ox < 8; ++ox) {
+                    if (icl == 0) { accb0 += d0[ox]; accb1 += d1[ox]; }
+#pragma unroll
+                    for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+                        for (int kx = 0; kx < 5; ++kx) {
+                            acc0[ky][kx] = fmaf(d0[ox], strip[ky][ox + kx], acc0[ky][kx]);
+                            acc1[ky][kx] = fmaf(d1[ox], strip[ky][ox + kx], acc1[ky][kx]);
+                        }
+                }
+            }
+        }
+    }
+    // ---- combine the two image-parity halves, then write the 50 x 100 tile coalesced ----
+    __syncthreads();
+    float *O_s = &D_s[0][0];  // [50 oc][100]  (+ 64 bias slots at 5000)
+    if (par == 1 && active) {
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx) {
+                O_s[lane * 100 + icl * 25 + ky * 5 + kx] = acc0[ky][kx];
+                O_s[(lane + 25) * 100 + icl * 25 + ky * 5 + kx] = acc1[ky][kx];
+            }
+        if (icl == 0) { O_s[5000 + lane] = accb0; O_s[5000 + lane + 25] = accb1; }
+    }
+    __syncthreads();
+    if (par == 0 && active) {
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx) {
+                O_s[lane * 100 + icl * 25 + ky * 5 + kx] += acc0[ky][kx];
+                O_s[(lane + 25) * 100 + icl * 25 + ky * 5 + kx] += acc1[ky][kx];
+            }
+        if (icl == 0) { O_s[5000 + lane] += accb0; O_s[5000 + lane + 25] += accb1; }
+    }
+    __syncthreads();
+    float *po = part + (size_t)blockIdx.y * kC2PartStride;
+    for (int i = tid; i < 5000; i += kWgThreads) {
+        const int oc = i / 100, m = i - oc * 100;
+        po[oc * 500 + ic0 * 25 + m] = O_s[i];
+    }
+    if (blockIdx.x == 0 && tid < 50) po[25024 + tid] = O_s[5000 + tid];
+}
+
+// ---------------------------------------------------------------------------------
+// conv1 weight/bias gradient (the input image needs no gradient).  The conv1 output
+// gradient has one non-zero per 2x2 window (pool arg-max) and none where ReLU was inactive,
+// so the sum is taken sparsely: warp = channel, lane = filter tap (25 active, lane 25 sums
+// the bias gradient); per window the gradient value and arg-max slot are fetched 32 at a
+// time and broadcast with shuffles, and windows with a zero gradient are skipped.
+// blockIdx.x slices the batch; each CTA writes a partial [512 + 64].
+// ---------------------------------------------------------------------------------
+constexpr int kC1wThreads = 640;
+constexpr int kC1PartStride = 576;  // 500 weights @0, 20 biases @512
+
+__global__ void __launch_bounds__(kC1wThreads)
+conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
+                   const uint8_t *__restrict__ i1, float *__restrict__ part, int B) {
+    __shared__ __align__(16) float xs[kXElems];
+    const int tid = threadIdx.x, c = tid >> 5, lane = tid & 31;
+    const int ky = lane / 5, kx = lane - ky * 5;  // lanes >= 25: unused taps
+    float acc = 0.f;
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+        __syncthreads();
+        for (int i = tid; i < kXElems / 4; i += kC1wThreads)
+            reinterpret_cast<float4 *>(xs)[i] = __ldg(reinterpret_cast<const float4 *>(x + (size_t)b * kXElems) + i);
+        __syncthreads();
+        const size_t base = ((size_t)b * 20 + c) * 144;
+        for (int w0 = 0; w0 < 144; w0 += 32) {
+            const int wl = w0 + lane;
+            float gl = 0.f;
+            int ol = 0;
+            if (wl < 144) {
+                const float pv = p1[base + wl];
+                if (pv > 0.f) gl = dp1[base + wl];
+                const int q = i1[base + wl];
+                ol = (2 * (wl / 12) + (q >> 1)) * 28 + 2 * (wl % 12) + (q & 1);
+            }
+            const int cnt = min(32, 144 - w0);
+            for (int j = 0; j < cnt; ++j) {
+                const float g = __shfl_sync(0xffffffffu, gl, j);
+                const int o = __shfl_sync(0xffffffffu, ol, j);
+                if (g != 0.f) {
+                    if (lane < 25) acc = fmaf(g, xs[o + ky * 28 + kx], acc);
+                    else if (lane == 25) acc += g;
+                }
+            }
+        }
+    }
+    float *po = part + (size_t)blockIdx.x * kC1PartStride;
+    if (lane < 25) po[c * 25 + lane] = acc;
+    else if (lane == 25) po[512 + c] = acc;
+}
+
+}  // namespace b200mnist

@@ -1,0 +1,293 @@
+"""``Net`` -- the reference's model (examples/mnist/mnist.py:17-33) on the B200 kernels.
+
+Same class name, same sub-module / parameter names (``conv1.weight`` ... ``fc2.bias``) and
+the same initial values for a given ``torch.manual_seed`` as the reference's ``Net``; the
+parameters, their gradients and the momentum buffers are views into three flat fp32
+buckets on the GPU so that the DDP exchange is one collective and the SGD update one kernel.
+
+Two ways to run a training step, both through libb200mnist.so (no torch math, no CPU
+fallback):
+  * the reference's own loop shape -- ``output = model(data); F.nll_loss(output, target)
+    .backward(); optimizer.step()`` -- via an autograd bridge over the per-layer entry points;
+  * ``model.train_step(data, target, optimizer)`` -- the fused step (one C call; captured in
+    a CUDA graph by ``StepGraph``), which ``mnist.train()`` uses.
+"""
+from __future__ import annotations
+
+import weakref
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+
+from . import _cabi
+
+NAMES = ["conv1.weight", "conv1.bias", "conv2.weight", "conv2.bias",
+         "fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias"]
+SHAPES = [(20, 1, 5, 5), (20,), (50, 20, 5, 5), (50,), (500, 800), (500,), (10, 500), (10,)]
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def flat_layout():
+    """[(name, shape, offset, numel)] of the flat bucket, as the library lays it out."""
+    L = _cabi.lib()
+    return [(n, s, int(L.b200mnist_tensor_offset(i)), int(L.b200mnist_tensor_elems(i)))
+            for i, (n, s) in enumerate(zip(NAMES, SHAPES))]
+
+
+class _Leaf(nn.Module):
+    """Holds ``weight`` and ``bias`` so state_dict keys match the reference's layers."""
+
+    def __init__(self):
+        super().__init__()
+        self.register_parameter("weight", None)
+        self.register_parameter("bias", None)
+
+
+class Net(nn.Module):
+    def __init__(self):
+        super().__init__()
+        # Build the reference's layers once on the CPU, in its declaration order
+        # (mnist.py:20-23), so the default init consumes the RNG stream identically.
+        ref_layers = [nn.Conv2d(1, 20, 5, 1), nn.Conv2d(20, 50, 5, 1), nn.Linear(4 * 4 * 50, 500), nn.Linear(500, 10)]
+        n = int(_cabi.lib().b200mnist_flat_elems())
+        flat = torch.zeros(n, dtype=torch.float32)
+        lay = flat_layout()
+        with torch.no_grad():
+            for li, layer in enumerate(ref_layers):
+                for pi, p in enumerate((layer.weight, layer.bias)):
+                    _, _, off, cnt = lay[2 * li + pi]
+                    flat[off:off + cnt] = p.reshape(-1)
+        self.conv1, self.conv2, self.fc1, self.fc2 = _Leaf(), _Leaf(), _Leaf(), _Leaf()
+        self._layout = lay
+        self._ddp = None          # set by ddp.DistributedDataParallel
+        self._ws = {}             # batch size -> workspace tensor
+        self._loss = None
+        self._bind(flat, torch.zeros_like(flat), torch.zeros_like(flat))
+
+    # ---- flat buckets and their named views -------------------------------------
+    def _bind(self, flat_p, flat_g, flat_m):
+        self.flat_params, self.flat_grads, self.flat_momentum = flat_p, flat_g, flat_m
+        leaves = (self.conv1, self.conv1, self.conv2, self.conv2, self.fc1, self.fc1, self.fc2, self.fc2)
+        for (name, shape, off, cnt), leaf in zip(self._layout, leaves):
+            attr = name.split(".")[1]
+            p = nn.Parameter(flat_p[off:off + cnt].view(shape), requires_grad=True)
+            p.grad = flat_g[off:off + cnt].view(shape)
+            p._b200_net = weakref.ref(self)  # lets optim.SGD(model.parameters(), ...) find the bucket
+            leaf._parameters[attr] = p
+        self._ws = {}
+        self._loss = torch.zeros(2, dtype=torch.float32, device=flat_p.device)
+
+    def _apply(self, fn, recurse=True):
+        # .to(device)/.cuda() must move the buckets and re-create the views, not the views.
+        self._bind(fn(self.flat_params), fn(self.flat_grads), fn(self.flat_momentum))
+        return self
+
+    @property
+    def device(self):
+        return self.flat_params.device
+
+    def named_views(self, flat):
+        return OrderedDict((name, flat[off:off + cnt].view(shape)) for name, shape, off, cnt in self._layout)
+
+    def load_named(self, named):
+        """Copy {name: tensor} (e.g. a reference state_dict or oracle params) into the bucket."""
+        with torch.no_grad():
+            for name, v in self.named_views(self.flat_params).items():
+                src = named[name] if name in named else named["module." + name]
+                v.copy_(torch.as_tensor(src).to(v.device, torch.float32).reshape(v.shape))
+
+    def workspace(self, batch: int) -> torch.Tensor:
+        ws = self._ws.get(batch)
+        if ws is None:
+            nbytes = int(_cabi.lib().b200mnist_workspace_bytes(batch))
+            if nbytes < 0:
+                raise ValueError(f"unsupported batch size {batch}")
+            ws = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)  # zero-filled once (ticket counters)
+            self._ws[batch] = ws
+        return ws
+
+    def _check_inputs(self, x, target=None):
+        if self.device.type != "cuda":
+            raise RuntimeError("Net runs on the CUDA kernels of libb200mnist.so only: move it with .to('cuda') "
+                               "(there is no CPU fallback)")
+        if x.device != self.device or x.dtype != torch.float32 or tuple(x.shape[1:]) != (1, 28, 28):
+            raise ValueError("data must be float32 [B,1,28,28] on the model's device")
+        if target is not None and (target.device != self.device or target.dtype != torch.int64
+                                   or target.shape != (x.shape[0],)):
+            raise ValueError("target must be int64 [B] on the model's device")
+        return x.contiguous()
+
+    # ---- reference-shaped forward (mnist.py:25-33) ---------------------------------
+    def forward(self, x):
+        x = self._check_inputs(x)
+        if torch.is_grad_enabled() and self.training:
+            params = [getattr(getattr(self, n.split(".")[0]), n.split(".")[1]) for n in NAMES]
+            return _LeNetFunction.apply(self, x, *params)
+        B = x.shape[0]
+        logp = torch.empty(B, 10, dtype=torch.float32, device=self.device)
+        dummy_t = torch.zeros(B, dtype=torch.int64, device=self.device)
+        ws = self.workspace(B)
+        L = _cabi.lib()
+        _cabi.check(L.b200mnist_forward_eval(self.flat_params.data_ptr(), x.data_ptr(), dummy_t.data_ptr(), B,
+                                             ws.data_ptr(), ws.numel(), logp.data_ptr(), self._loss.data_ptr(),
+                                             _stream()), "forward_eval")
+        return logp
+
+    # ---- fused entry points -----------------------------------------------------
+    def forward_backward(self, x, target, logp_out=None):
+        """mnist.py:39-42 in one call: fills ``flat_grads`` (this rank's gradient) and returns
+        the mean-NLL loss as a 0-d device tensor (no sync)."""
+        x = self._check_inputs(x, target)
+        B = x.shape[0]
+        ws = self.workspace(B)
+        L = _cabi.lib()
+        _cabi.check(L.b200mnist_forward_backward(self.flat_params.data_ptr(), self.flat_grads.data_ptr(),
+                                                 x.data_ptr(), target.data_ptr(), B, ws.data_ptr(), ws.numel(),
+                                                 self._loss.data_ptr(), _cabi.ptr(logp_out), _stream()),
+                    "forward_backward")
+        return self._loss[0]
+
+    def train_step(self, x, target, optimizer):
+        """mnist.py:39-43 in one call.  With DDP attached the gradient bucket is all-reduced
+        between the backward and the update, and 1/world_size is folded into the update."""
+        if self._ddp is None:
+            x = self._check_inputs(x, target)
+            B = x.shape[0]
+            ws = self.workspace(B)
+            L = _cabi.lib()
+            _cabi.check(L.b200mnist_train_step(self.flat_params.data_ptr(), self.flat_grads.data_ptr(),
+                                               self.flat_momentum.data_ptr(), x.data_ptr(), target.data_ptr(), B,
+                                               ws.data_ptr(), ws.numel(), optimizer.lr, optimizer.momentum,
+                                               1 if optimizer.first_step else 0, self._loss.data_ptr(), _stream()),
+                        "train_step")
+            optimizer.first_step = False
+            return self._loss[0]
+        loss = self.forward_backward(x, target)
+        self._ddp.reduce_gradients()
+        optimizer.step()
+        return loss
+
+    def evaluate(self, x, target, stats_out=None, logp_out=None):
+        """One batch of test() (mnist.py:56-61): returns a device tensor [nll_sum, n_correct]."""
+        x = self._check_inputs(x, target)
+        B = x.shape[0]
+        ws = self.workspace(B)
+        if stats_out is None:
+            stats_out = torch.zeros(2, dtype=torch.float32, device=self.device)
+        L = _cabi.lib()
+        _cabi.check(L.b200mnist_forward_eval(self.flat_params.data_ptr(), x.data_ptr(), target.data_ptr(), B,
+                                             ws.data_ptr(), ws.numel(), _cabi.ptr(logp_out), stats_out.data_ptr(),
+                                             _stream()), "forward_eval")
+        return stats_out
+
+
+class _LeNetFunction(torch.autograd.Function):
+    """Autograd bridge: the whole Net as one node, forward and backward on the per-layer
+    entry points.  Parameter gradients are written straight into the flat gradient bucket
+    (overwritten, as after the reference's zero_grad(); not accumulated)."""
+
+    @staticmethod
+    def forward(ctx, net, x, *params):
+        L, s, dev, B = _cabi.lib(), _stream(), x.device, x.shape[0]
+        P = net.named_views(net.flat_params)
+        f32 = dict(dtype=torch.float32, device=dev)
+        p1 = torch.empty(B, 20, 12, 12, **f32)
+        i1 = torch.empty(B, 20, 12, 12, dtype=torch.uint8, device=dev)
+        p2 = torch.empty(B, 50, 4, 4, **f32)
+        i2 = torch.empty(B, 50, 4, 4, dtype=torch.uint8, device=dev)
+        h = torch.empty(B, 500, **f32)
+        logp = torch.empty(B, 10, **f32)
+        scratch = torch.zeros(int(L.b200mnist_fc1_scratch_bytes(B)) // 4, **f32)
+        _cabi.check(L.b200mnist_conv1_relu_pool_fwd(x.data_ptr(), P["conv1.weight"].data_ptr(),
+                                                    P["conv1.bias"].data_ptr(), p1.data_ptr(), i1.data_ptr(), B, s),
+                    "conv1 fwd")
+        _cabi.check(L.b200mnist_conv2_relu_pool_fwd(p1.data_ptr(), P["conv2.weight"].data_ptr(),
+                                                    P["conv2.bias"].data_ptr(), p2.data_ptr(), i2.data_ptr(), B, s),
+                    "conv2 fwd")
+        _cabi.check(L.b200mnist_fc1_relu_fwd(p2.data_ptr(), P["fc1.weight"].data_ptr(), P["fc1.bias"].data_ptr(),
+                                             h.data_ptr(), B, scratch.data_ptr(), s), "fc1 fwd")
+        # fc2 + log_softmax through the head kernel (targets unused here: zeros)
+        t0 = torch.zeros(B, dtype=torch.int64, device=dev)
+        hs = torch.zeros(B + 64, **f32)
+        loss = torch.empty(1, **f32)
+        _cabi.check(L.b200mnist_fc2_logsoftmax_nll(h.data_ptr(), P["fc2.weight"].data_ptr(), P["fc2.bias"].data_ptr(),
+                                                   t0.data_ptr(), B, logp.data_ptr(), loss.data_ptr(), 0, 0,
+                                                   hs.data_ptr(), s), "head fwd")
+        ctx.net = net
+        ctx.save_for_backward(x, p1, i1, p2, i2, h, logp)
+        return logp
+
+    @staticmethod
+    def backward(ctx, dlogp):
+        net = ctx.net
+        x, p1, i1, p2, i2, h, logp = ctx.saved_tensors
+        L, s, dev, B = _cabi.lib(), _stream(), x.device, x.shape[0]
+        P, G = net.named_views(net.flat_params), net.named_views(net.flat_grads)
+        f32 = dict(dtype=torch.float32, device=dev)
+        dlogp = dlogp.contiguous().to(torch.float32)
+        dz2, dz1 = torch.empty(B, 10, **f32), torch.empty(B, 500, **f32)
+        dp2, dp1 = torch.empty(B, 800, **f32), torch.empty(B, 20, 12, 12, **f32)
+        _cabi.check(L.b200mnist_head_bwd(logp.data_ptr(), dlogp.data_ptr(), h.data_ptr(), P["fc2.weight"].data_ptr(),
+                                         B, dz2.data_ptr(), dz1.data_ptr(), s), "head bwd")
+        sc = torch.empty(int(L.b200mnist_fc_bwd_scratch_bytes(B)), dtype=torch.uint8, device=dev)
+        _cabi.check(L.b200mnist_fc_bwd(dz2.data_ptr(), dz1.data_ptr(), h.data_ptr(), p2.data_ptr(),
+                                       P["fc1.weight"].data_ptr(), B, G["fc2.weight"].data_ptr(),
+                                       G["fc2.bias"].data_ptr(), G["fc1.weight"].data_ptr(), G["fc1.bias"].data_ptr(),
+                                       dp2.data_ptr(), sc.data_ptr(), s), "fc bwd")
+        sc2 = torch.empty(int(L.b200mnist_conv2_bwd_scratch_bytes(B)), dtype=torch.uint8, device=dev)
+        _cabi.check(L.b200mnist_conv2_bwd(dp2.data_ptr(), p2.data_ptr(), i2.data_ptr(), p1.data_ptr(),
+                                          P["conv2.weight"].data_ptr(), B, G["conv2.weight"].data_ptr(),
+                                          G["conv2.bias"].data_ptr(), dp1.data_ptr(), sc2.data_ptr(), s), "conv2 bwd")
+        sc1 = torch.empty(int(L.b200mnist_conv1_bwd_scratch_bytes(B)), dtype=torch.uint8, device=dev)
+        _cabi.check(L.b200mnist_conv1_bwd(dp1.data_ptr(), p1.data_ptr(), i1.data_ptr(), x.data_ptr(), B,
+                                          G["conv1.weight"].data_ptr(), G["conv1.bias"].data_ptr(), sc1.data_ptr(), s),
+                    "conv1 bwd")
+        for name in NAMES:  # re-attach the views in case zero_grad() set them to None
+            mod, attr = name.split(".")
+            getattr(getattr(net, mod), attr).grad = G[name]
+        if net._ddp is not None:
+            net._ddp.reduce_gradients()
+        return (None, None) + (None,) * 8
+
+
+class StepGraph:
+    """The fused training step captured once in a CUDA graph and replayed per batch
+    (the B=64 step is launch-latency bound: ~10 kernels of a few microseconds each).
+    Static input buffers ``x``/``target`` are filled by the caller (e.g. an H2D copy) before
+    ``replay()``; ``loss`` is a 0-d view of the device scalar the graph writes."""
+
+    def __init__(self, model: Net, optimizer, batch: int):
+        if optimizer.first_step:
+            raise RuntimeError("run one eager step first (the first SGD step initialises the momentum buffer)")
+        model = getattr(model, "module", model)  # accept our DistributedDataParallel wrapper
+        dev = model.device
+        self.model, self.optimizer = model, optimizer
+        self.x = torch.zeros(batch, 1, 28, 28, dtype=torch.float32, device=dev)
+        self.target = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.lr, self.momentum = optimizer.lr, optimizer.momentum
+        model.workspace(batch)  # allocate outside capture
+        self.graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        # Warm-up on the capture stream (lazy CUDA/NCCL initialisation must happen outside the
+        # capture); it is a real step on zero data, so the training state is put back afterwards.
+        saved = [t.clone() for t in (model.flat_params, model.flat_grads, model.flat_momentum)]
+        with torch.cuda.stream(side):
+            model.train_step(self.x, self.target, optimizer)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize(dev)
+        for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum), saved):
+            t.copy_(sv)
+        torch.cuda.synchronize(dev)
+        with torch.cuda.graph(self.graph, stream=side):
+            self.loss = model.train_step(self.x, self.target, optimizer)
+
+    def replay(self):
+        if (self.optimizer.lr, self.optimizer.momentum) != (self.lr, self.momentum):
+            raise RuntimeError("lr/momentum changed after capture; build a new StepGraph")
+        self.graph.replay()
+        return self.loss

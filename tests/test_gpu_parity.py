@@ -1,0 +1,274 @@
+"""Parity of the CUDA path (through the C ABI of libb200mnist.so) with the CPU oracle and with
+the fixtures produced by the unmodified reference.  Run on the B200 box: pytest -m gpu.
+
+Tolerance (north_star: "1e-5 relative on per-step loss and gradients"): |a-b| <= 1e-5*|b| +
+1e-5*max|b| per tensor (tests/helpers.py).  SGD and the smoke-dist square are bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import c_oracle, mnist_oracle as mo
+from tests.helpers import NAMES, RTOL, assert_close, batch_seed, golden_tensor_check, load_golden
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import pytorch_operator_b200 as pkg
+    from pytorch_operator_b200 import _cabi
+DEV = "cuda:0"
+
+
+def _net(seed=1):
+    torch.manual_seed(seed)
+    return pkg.Net().to(DEV)
+
+
+def _grads(net):
+    return {k: v.detach().cpu().numpy() for k, v in net.named_views(net.flat_grads).items()}
+
+
+def _params(net):
+    return {k: v.detach().cpu().numpy() for k, v in net.named_views(net.flat_params).items()}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def test_library_loaded_and_no_cpu_fallback():
+    assert _cabi.lib().b200mnist_version() >= 100
+    cpu_net = pkg.Net()
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        cpu_net(torch.zeros(1, 1, 28, 28))
+
+
+@pytest.mark.parametrize("B", [1, 5, 64])
+def test_forward_layers_match_c_oracle(B):
+    L = _cabi.lib()
+    params = {k: v.numpy() for k, v in mo.init_params(1).items()}
+    x, _ = mo.synthetic_batch(B, 99 + B)
+    act = c_oracle.forward(params, x.numpy())
+    d = {k: torch.from_numpy(np.ascontiguousarray(v)).to(DEV) for k, v in params.items()}
+    xd = x.to(DEV)
+    p1 = torch.empty(B, 20, 12, 12, device=DEV)
+    i1 = torch.empty(B, 20, 12, 12, dtype=torch.uint8, device=DEV)
+    _cabi.check(L.b200mnist_conv1_relu_pool_fwd(xd.data_ptr(), d["conv1.weight"].data_ptr(), d["conv1.bias"].data_ptr(),
+                                                p1.data_ptr(), i1.data_ptr(), B, _stream()), "conv1")
+    assert_close(p1.cpu().numpy(), act["p1"], what="p1")
+    live = act["p1"] > 1e-4  # arg-max is only defined (and only used) where the ReLU output is positive
+    assert np.array_equal(i1.cpu().numpy()[live], act["i1"][live])
+    p1o = torch.from_numpy(act["p1"]).to(DEV)
+    p2 = torch.empty(B, 50, 4, 4, device=DEV)
+    i2 = torch.empty(B, 50, 4, 4, dtype=torch.uint8, device=DEV)
+    _cabi.check(L.b200mnist_conv2_relu_pool_fwd(p1o.data_ptr(), d["conv2.weight"].data_ptr(), d["conv2.bias"].data_ptr(),
+                                                p2.data_ptr(), i2.data_ptr(), B, _stream()), "conv2")
+    assert_close(p2.cpu().numpy(), act["p2"], what="p2")
+    live = act["p2"] > 1e-4
+    assert np.array_equal(i2.cpu().numpy()[live], act["i2"][live])
+    p2o = torch.from_numpy(act["p2"]).to(DEV)
+    h = torch.empty(B, 500, device=DEV)
+    sc = torch.zeros(int(L.b200mnist_fc1_scratch_bytes(B)), dtype=torch.uint8, device=DEV)
+    _cabi.check(L.b200mnist_fc1_relu_fwd(p2o.data_ptr(), d["fc1.weight"].data_ptr(), d["fc1.bias"].data_ptr(),
+                                         h.data_ptr(), B, sc.data_ptr(), _stream()), "fc1")
+    assert_close(h.cpu().numpy(), act["h"], what="h")
+
+
+@pytest.mark.parametrize("B", [1, 2, 5, 63, 64, 65, 200])
+def test_forward_backward_matches_oracles(B):
+    net = _net()
+    x, t = mo.synthetic_batch(B, 500 + B)
+    logp = torch.empty(B, 10, device=DEV)
+    loss = net.forward_backward(x.to(DEV), t.to(DEV), logp_out=logp)
+    params = mo.init_params(1)
+    lo, logp_o, g_o = mo.loss_and_grads(params, x, t)
+    assert abs(float(loss) - float(lo)) <= RTOL * abs(float(lo)) * 2
+    assert_close(logp.cpu().numpy(), logp_o.numpy(), what="logp")
+    got = _grads(net)
+    for n in NAMES:
+        assert_close(got[n], g_o[n].numpy(), what=f"grad {n} (torch oracle)")
+    if B <= 64:
+        lc, _, g_c = c_oracle.loss_and_grads({k: v.numpy() for k, v in params.items()}, x.numpy(), t.numpy())
+        assert abs(float(loss) - lc) <= RTOL * abs(lc) * 2
+        for n in NAMES:
+            assert_close(got[n], g_c[n], what=f"grad {n} (C oracle)")
+    # pad elements of the bucket stay zero
+    total = sum(v.size for v in got.values())
+    assert abs(float(net.flat_grads.double().abs().sum()) - sum(float(np.abs(v.astype(np.float64)).sum()) for v in got.values())) < 1e-6 * total
+
+
+def test_step0_gradients_match_reference_fixture():
+    gold = load_golden("train_ws1_b64")
+    net = _net()
+    x, t = mo.synthetic_batch(64, batch_seed(0, 0))
+    loss = net.forward_backward(x.to(DEV), t.to(DEV))
+    assert abs(float(loss) - float(gold["step0/loss_rank0"][0])) <= RTOL * 2.4
+    for n, v in _grads(net).items():
+        golden_tensor_check(gold, "step0/grad", n, v)
+
+
+@pytest.mark.parametrize("case,graph", [("train_ws1_b64", False), ("train_ws1_b64", True), ("train_ws1_b5", False)])
+def test_free_running_training_matches_reference_fixture(case, graph):
+    """3 (or 1) full steps -- fused forward/backward/SGD, eager and CUDA-graph replay -- against the
+    losses, gradients and updated parameters the reference's train() produced."""
+    gold = load_golden(case)
+    B, nsteps = int(gold["meta/batch_size"][0]), int(gold["meta/nsteps"][0])
+    net = _net()
+    opt = pkg.SGD(net.parameters(), lr=0.01, momentum=0.5)
+    g = None
+    for s in range(nsteps):
+        x, t = mo.synthetic_batch(B, batch_seed(s, 0))
+        if graph and s > 0:
+            g = g or pkg.StepGraph(net, opt, B)
+            g.x.copy_(x)
+            g.target.copy_(t)
+            loss = g.replay()
+        else:
+            loss = net.train_step(x.to(DEV), t.to(DEV), opt)
+        # free-running: step s sees parameters that already carry fp32 noise from earlier steps
+        assert abs(float(loss) - float(gold[f"step{s}/loss_rank0"][0])) <= 4 * RTOL * 2.4
+        for n, v in _grads(net).items():
+            golden_tensor_check(gold, f"step{s}/grad", n, v, rtol=4 * RTOL)
+        for n, v in _params(net).items():
+            golden_tensor_check(gold, f"step{s}/param", n, v, rtol=RTOL)
+
+
+def test_reference_shaped_loop_through_autograd_bridge():
+    """output = model(data); F.nll_loss(output, target).backward(); optimizer.step() -- the loop
+    body of the reference's train() verbatim -- gives the same gradients as the fused call."""
+    import torch.nn.functional as F
+    gold = load_golden("train_ws1_b64")
+    net = _net()
+    opt = pkg.SGD(net.parameters(), lr=0.01, momentum=0.5)
+    for s in range(2):
+        x, t = mo.synthetic_batch(64, batch_seed(s, 0))
+        data, target = x.to(DEV), t.to(DEV)
+        opt.zero_grad()
+        output = net(data)
+        loss = F.nll_loss(output, target)
+        loss.backward()
+        for n, p in net.named_parameters():
+            golden_tensor_check(gold, f"step{s}/grad", n, p.grad.cpu().numpy(), rtol=4 * RTOL)
+        opt.step()
+        assert abs(loss.item() - float(gold[f"step{s}/loss_rank0"][0])) <= 4 * RTOL * 2.4
+        for n, v in _params(net).items():
+            golden_tensor_check(gold, f"step{s}/param", n, v)
+
+
+def test_sgd_bit_exact_vs_torch_and_c_oracle():
+    n = 431296
+    g = torch.Generator().manual_seed(3)
+    p0 = torch.randn(n, generator=g)
+    p_t = p0.clone().requires_grad_(True)
+    opt = torch.optim.SGD([p_t], lr=0.01, momentum=0.5)
+    p_d, m_d = p0.to(DEV), torch.zeros(n, device=DEV)
+    p_c, m_c = p0.numpy().copy(), np.zeros(n, np.float32)
+    L = _cabi.lib()
+    for step in range(3):
+        grad = torch.randn(n, generator=g)
+        p_t.grad = (grad * 0.25).clone()  # DDP mean over 4 ranks: exact power-of-two scale
+        opt.step()
+        gd = grad.to(DEV)
+        _cabi.check(L.b200mnist_sgd_momentum(p_d.data_ptr(), gd.data_ptr(), m_d.data_ptr(), n, 0.01, 0.5, 0.25,
+                                             1 if step == 0 else 0, _stream()), "sgd")
+        c_oracle.sgd_momentum_(p_c, grad.numpy(), m_c, 0.01, 0.5, 0.25, step == 0)
+        assert torch.equal(p_d.cpu(), p_t.detach()), f"step {step} vs torch.optim.SGD"
+        assert np.array_equal(p_d.cpu().numpy(), p_c), f"step {step} vs C oracle"
+    # ragged length / empty input
+    for m in (0, 1, 3, 1023, 1025):
+        a, b, c = torch.ones(max(m, 4), device=DEV), torch.ones(max(m, 4), device=DEV), torch.zeros(max(m, 4), device=DEV)
+        _cabi.check(L.b200mnist_sgd_momentum(a.data_ptr(), b.data_ptr(), c.data_ptr(), m, 0.5, 0.0, 1.0, 1, _stream()), "sgd")
+        assert torch.equal(a.cpu()[:m], torch.full((m,), 0.5)) and torch.equal(a.cpu()[m:], torch.ones(max(m, 4) - m))
+
+
+def test_eval_matches_reference_fixture():
+    gold = load_golden("eval_b1000")
+    net = _net()
+    net.eval()
+    totals = torch.zeros(2, dtype=torch.float64, device=DEV)
+    for i, seed in enumerate((4321, 4322)):
+        x, t = mo.synthetic_batch(1000, seed)
+        if i == 0:
+            with torch.no_grad():
+                logp = net(x.to(DEV))
+            assert_close(logp.cpu().numpy(), gold["logp_batch0"], what="logp")
+            nll_o, correct_o, _ = mo.evaluate(mo.init_params(1), x, t)
+            st = net.evaluate(x.to(DEV), t.to(DEV)).cpu()
+            assert abs(float(st[0]) - nll_o) <= RTOL * nll_o * 2 and int(st[1]) == correct_o
+        totals += net.evaluate(x.to(DEV), t.to(DEV)).double()
+    assert float(totals[1]) / 2000.0 == float(gold["accuracy"][0])
+
+
+def test_square_bit_exact_and_smoke_fixture():
+    from pytorch_operator_b200.dist_sendrecv import square
+    gold = load_golden("smoke_sendrecv_ws3")
+    inp = torch.from_numpy(gold["inp"])
+    out = square(inp.to(DEV)).cpu()
+    assert np.array_equal(out.numpy(), gold["result_from_worker1"])
+    g = torch.Generator().manual_seed(11)
+    for n in (1, 255, 257, 100003):
+        v = torch.randn(n, generator=g) * 1e3
+        assert torch.equal(square(v.to(DEV)).cpu(), torch.mul(v, v))
+    assert square(torch.empty(0, device=DEV)).numel() == 0
+
+
+def test_full_size_batch_properties():
+    """BASELINE config 5 size (B=4096): results are checked through size-independent properties --
+    the batch gradient is the mean of the chunk gradients (linearity of the mean loss), the run
+    is bitwise repeatable, and the loss is the mean of the chunk losses."""
+    B, C = 4096, 512
+    net = _net()
+    x, t = mo.synthetic_batch(B, 777)
+    xd, td = x.to(DEV), t.to(DEV)
+    loss = float(net.forward_backward(xd, td))
+    g_full = net.flat_grads.clone()
+    loss2 = float(net.forward_backward(xd, td))
+    assert loss == loss2 and torch.equal(g_full, net.flat_grads), "not bitwise repeatable"
+    acc = torch.zeros_like(g_full, dtype=torch.float64)
+    lsum = 0.0
+    for c in range(0, B, C):
+        lsum += float(net.forward_backward(xd[c:c + C], td[c:c + C]))
+        acc += net.flat_grads.double()
+    assert abs(loss - lsum / (B // C)) <= RTOL * abs(loss)
+    assert_close(g_full.cpu().numpy(), (acc / (B // C)).cpu().numpy(), rtol=2 * RTOL, what="batch-additivity")
+    # and one chunk against the CPU oracle
+    lo, _, g_o = mo.loss_and_grads(mo.init_params(1), x[:C], t[:C])
+    l1 = float(net.forward_backward(xd[:C], td[:C]))
+    assert abs(l1 - float(lo)) <= RTOL * abs(float(lo)) * 2
+    for n, v in _grads(net).items():
+        assert_close(v, g_o[n].numpy(), what=f"B=512 grad {n}")
+
+
+def test_argument_errors_and_bad_target():
+    L = _cabi.lib()
+    net = _net()
+    x, t = mo.synthetic_batch(4, 5)
+    xd, td = x.to(DEV), t.to(DEV)
+    ws = net.workspace(4)
+    rc = L.b200mnist_forward_backward(net.flat_params.data_ptr(), net.flat_grads.data_ptr(), xd.data_ptr(),
+                                      td.data_ptr(), 8, ws.data_ptr(), ws.numel(), net._loss.data_ptr(), 0, _stream())
+    assert rc == -10004 and "workspace" in _cabi.last_error()
+    rc = L.b200mnist_forward_backward(0, net.flat_grads.data_ptr(), xd.data_ptr(), td.data_ptr(), 4, ws.data_ptr(),
+                                      ws.numel(), net._loss.data_ptr(), 0, _stream())
+    assert rc == -10001
+    rc = L.b200mnist_forward_backward(net.flat_params.data_ptr(), net.flat_grads.data_ptr(), xd.data_ptr(),
+                                      td.data_ptr(), 0, ws.data_ptr(), ws.numel(), net._loss.data_ptr(), 0, _stream())
+    assert rc == -10002
+    with pytest.raises(ValueError):
+        net.forward_backward(xd.double(), td)
+    td_bad = td.clone()
+    td_bad[2] = 10  # torch raises "Target 10 is out of bounds"; the kernel poisons the loss instead
+    assert np.isnan(float(net.forward_backward(xd, td_bad)))
+    assert np.isfinite(float(net.forward_backward(xd, td)))
+
+
+def test_state_dict_roundtrip_and_device_move():
+    net = _net()
+    sd = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    assert list(sd) == NAMES
+    ref = mo.init_params(1)
+    assert all(torch.equal(sd[k], ref[k]) for k in NAMES)
+    other = _net(seed=2)
+    other.load_named(sd)
+    assert torch.equal(other.flat_params, net.flat_params)
+    for n, p in net.named_parameters():  # views alias the bucket after .to()
+        assert p.data_ptr() >= net.flat_params.data_ptr() and p.grad.data_ptr() >= net.flat_grads.data_ptr()

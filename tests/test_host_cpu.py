@@ -1,0 +1,162 @@
+"""CPU-only checks (pytest -m "not gpu"): the C-ABI library loads and exports every symbol the
+header declares, host-side argument validation, the operator env contract, the payload CLI,
+and the world_size-2 host logic of the flat-bucket DDP on gloo.  No kernel is launched here."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import pytorch_operator_b200 as pkg
+from pytorch_operator_b200 import _cabi, launcher
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "b200mnist.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200mnist_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(_cabi.build())
+    names = _header_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/b200mnist.h but not exported"
+    assert set(names) == set(_cabi.SIGNATURES), "ctypes signature table out of sync with the header"
+
+
+def test_flat_layout_is_aligned_and_complete():
+    L = _cabi.lib()
+    assert L.b200mnist_flat_elems() == 431296
+    end = 0
+    total = 0
+    for i, shape in enumerate(pkg.net.SHAPES):
+        off, cnt = L.b200mnist_tensor_offset(i), L.b200mnist_tensor_elems(i)
+        assert cnt == int(np.prod(shape)) and off % 64 == 0 and off >= end
+        end = off + cnt
+        total += cnt
+    assert total == 431080 and end <= 431296
+    assert L.b200mnist_tensor_offset(8) == -1 and L.b200mnist_tensor_elems(-1) == -1
+
+
+def test_argument_validation_without_a_gpu():
+    L = _cabi.lib()
+    assert L.b200mnist_workspace_bytes(0) == -1 and L.b200mnist_workspace_bytes(64) > 64 * 2880 * 4
+    assert L.b200mnist_workspace_bytes(64) % 256 == 0
+    assert L.b200mnist_sgd_momentum(0, 0, 0, 10, 0.1, 0.5, 1.0, 1, 0) == -10001
+    assert "null" in _cabi.last_error()
+    assert L.b200mnist_sgd_momentum(16, 16, 16, -1, 0.1, 0.5, 1.0, 1, 0) == -10002
+    assert L.b200mnist_sgd_momentum(16, 20, 16, 4, 0.1, 0.5, 1.0, 1, 0) == -10003  # misaligned
+    assert L.b200mnist_sgd_momentum(16, 16, 16, 0, 0.1, 0.5, 1.0, 1, 0) == 0       # empty input is a no-op
+    assert L.b200mnist_square(0, 0, 0, 0) == 0
+    assert L.b200mnist_conv1_relu_pool_fwd(16, 16, 16, 16, 16, 0, 0) == -10002
+    assert L.b200mnist_forward_backward(16, 16, 16, 16, 70000, 256, 1 << 40, 16, 0, 0) == -10002
+
+
+def test_net_mirrors_reference_module_without_a_gpu():
+    torch.manual_seed(1)
+    net = pkg.Net()
+    ref = torch.nn.Sequential()  # reference layer order, same seed
+    torch.manual_seed(1)
+    layers = [torch.nn.Conv2d(1, 20, 5, 1), torch.nn.Conv2d(20, 50, 5, 1), torch.nn.Linear(800, 500),
+              torch.nn.Linear(500, 10)]
+    want = {}
+    for name, l in zip(("conv1", "conv2", "fc1", "fc2"), layers):
+        want[name + ".weight"], want[name + ".bias"] = l.weight, l.bias
+    sd = net.state_dict()
+    assert list(sd) == pkg.NAMES
+    for k in pkg.NAMES:
+        assert torch.equal(sd[k], want[k].detach())
+    assert sum(p.numel() for p in net.parameters()) == 431080
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        net(torch.zeros(2, 1, 28, 28))
+    opt = pkg.SGD(net.parameters(), lr=0.01, momentum=0.5)
+    assert opt.model is net and opt.first_step
+    with pytest.raises(ValueError):
+        pkg.SGD([torch.nn.Parameter(torch.zeros(3))], lr=0.1)
+
+
+# ---- operator env contract: golden values of TestClusterSpec, pod_test.go:108-150 ----
+@pytest.mark.parametrize("workers,rtype,index,expect", [
+    (0, "Master", 0, {"WORLD_SIZE": "1", "MASTER_PORT": "23456", "RANK": "0", "MASTER_ADDR": "localhost"}),
+    (1, "Master", 0, {"WORLD_SIZE": "2", "MASTER_PORT": "23456", "RANK": "0", "MASTER_ADDR": "localhost"}),
+    (1, "Worker", 0, {"WORLD_SIZE": "2", "MASTER_PORT": "23456", "RANK": "1", "MASTER_ADDR": "test-pytorchjob-master-0"}),
+    (2, "Master", 0, {"WORLD_SIZE": "3", "MASTER_PORT": "23456", "RANK": "0", "MASTER_ADDR": "localhost"}),
+    (2, "Worker", 0, {"WORLD_SIZE": "3", "MASTER_PORT": "23456", "RANK": "1", "MASTER_ADDR": "test-pytorchjob-master-0"}),
+    (2, "Worker", 1, {"WORLD_SIZE": "3", "MASTER_PORT": "23456", "RANK": "2", "MASTER_ADDR": "test-pytorchjob-master-0"}),
+])
+def test_cluster_spec_matches_operator_golden(workers, rtype, index, expect):
+    env = launcher.cluster_spec("test-pytorchjob", workers, rtype, index)
+    for k, v in expect.items():
+        assert env[k] == v
+    assert env["PYTHONUNBUFFERED"] == "0"
+
+
+def test_cluster_spec_rejects_second_master():
+    with pytest.raises(ValueError):
+        launcher.cluster_spec("j", 1, "Master", 1)
+
+
+def test_payload_cli_and_helpers():
+    env = dict(os.environ, WORLD_SIZE="2", PYTHONPATH=ROOT)
+    code = ("import pytorch_operator_b200.mnist as m; print(m.WORLD_SIZE, m.should_distribute(), m.is_distributed());"
+            "import inspect; print(list(inspect.signature(m.train).parameters));"
+            "print(list(inspect.signature(m.test).parameters))")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True).stdout
+    lines = out.strip().splitlines()
+    assert lines[0] == "2 True False"
+    assert lines[1] == str(["args", "model", "device", "train_loader", "optimizer", "epoch", "writer"])
+    assert lines[2] == str(["args", "model", "device", "test_loader", "writer", "epoch"])
+    # no GPU here: the payload must refuse to run rather than fall back to the CPU
+    r = subprocess.run([sys.executable, "-m", "pytorch_operator_b200.mnist", "--synthetic", "2"],
+                       env=dict(os.environ, PYTHONPATH=ROOT, WORLD_SIZE="1"), capture_output=True, text=True)
+    if not torch.cuda.is_available():
+        assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
+    r = subprocess.run([sys.executable, "-m", "pytorch_operator_b200.mnist", "--help"],
+                       env=dict(os.environ, PYTHONPATH=ROOT), capture_output=True, text=True, check=True)
+    for flag in ("--batch-size", "--test-batch-size", "--epochs", "--lr", "--momentum", "--no-cuda", "--seed",
+                 "--log-interval", "--save-model", "--dir", "--backend"):
+        assert flag in r.stdout
+
+
+def _ddp_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(launcher.cluster_spec("t", world - 1, "master" if rank == 0 else "worker", max(rank - 1, 0), port))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    dist.init_process_group("gloo")
+    torch.manual_seed(100 + rank)  # different initial weights per rank: the ctor broadcast must fix that
+    net = pkg.Net()
+    ddp = pkg.DistributedDataParallel(net)
+    opt = pkg.SGD(ddp.parameters(), lr=0.01, momentum=0.5)
+    torch.manual_seed(100)
+    want = pkg.Net().flat_params
+    ok_bcast = torch.equal(net.flat_params, want)
+    net.flat_grads.copy_(torch.arange(net.flat_grads.numel(), dtype=torch.float32) % 7 + rank)
+    ddp.reduce_gradients()
+    expect = (torch.arange(net.flat_grads.numel(), dtype=torch.float32) % 7) * world + sum(range(world))
+    ok_sum = torch.equal(net.flat_grads, expect)
+    ok_views = torch.equal(net.fc2.bias.grad, expect[431232:431242])
+    q.put((rank, ok_bcast, ok_sum, ok_views, opt.effective_grad_scale(), list(ddp.state_dict())[0]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_flat_bucket_ddp_host_logic_world_size_2_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_ddp_worker, args=(r, 2, 29641, q)) for r in range(2)]
+    [p.start() for p in procs]
+    res = sorted(q.get(timeout=120) for _ in procs)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    for rank, ok_bcast, ok_sum, ok_views, scale, first_key in res:
+        assert ok_bcast and ok_sum and ok_views, (rank, ok_bcast, ok_sum, ok_views)
+        assert scale == 0.5 and first_key == "module.conv1.weight"
