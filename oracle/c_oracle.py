@@ -52,11 +52,15 @@ def forward(params, x):
     return act
 
 
-def loss_and_grads(params, x, target):
+def loss_and_grads(params, x, target, idx_override=None):
     """Returns (loss, logp, grads dict) for one batch; the C analogue of
-    mnist_oracle.loss_and_grads."""
+    mnist_oracle.loss_and_grads.  ``idx_override=(i1, i2)`` teacher-forces the max-pool
+    arg-max maps used by the backward (see mnist_oracle.pool_tie_gap)."""
     B = int(x.shape[0])
     act = forward(params, x)
+    if idx_override is not None:
+        act["i1"] = np.ascontiguousarray(idx_override[0], dtype=np.uint8).reshape(act["i1"].shape)
+        act["i2"] = np.ascontiguousarray(idx_override[1], dtype=np.uint8).reshape(act["i2"].shape)
     t = np.ascontiguousarray(target, dtype=np.int64)
     vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)
     loss = lib().lenet_nll_mean(vp(act["logp"]), vp(t), ctypes.c_int(B))

@@ -69,6 +69,24 @@ def batch_seed(step: int, rank: int) -> int:
     return 1234 + 97 * step + rank
 
 
+MIN_POOL_GAP = 5e-7
+
+
+def tie_safe_batch(named_params, batch_size, step, rank):
+    """First seed batch_seed(step, rank) + 1000*k whose batch has no max-pool near-tie under the
+    current parameters (mnist_oracle.pool_tie_gap): where two window candidates differ by less
+    than fp32 summation noise, the arg-max the reference routes the gradient to is an accident
+    of its summation order and no other implementation can be expected to reproduce it."""
+    from oracle.mnist_oracle import pool_tie_gap, synthetic_batch
+    params = {k.replace("module.", ""): v.detach() for k, v in named_params}
+    for k in range(2000):
+        seed = batch_seed(step, rank) + 1000 * k
+        x, t = synthetic_batch(batch_size, seed)
+        if pool_tie_gap(params, x) >= MIN_POOL_GAP:
+            return seed, x, t
+    raise RuntimeError("no tie-safe seed found")
+
+
 def _pack(prefix, named, out):
     for k, v in named.items():
         a = v.detach().cpu().numpy().astype(np.float32)
@@ -102,7 +120,9 @@ def _train_case(rank, world_size, batch_size, nsteps, port, result_path):
     opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.5)  # mnist.py:140 defaults
     writer = _RecordingWriter()
     for s in range(nsteps):
-        loader = _Loader([synthetic_batch(batch_size, batch_seed(s, rank))])
+        seed, x, t = tie_safe_batch(model.named_parameters(), batch_size, s, rank)
+        out[f"step{s}/seed_rank{rank}"] = np.array([seed])
+        loader = _Loader([(x, t)])
         ref.train(_args(), model, torch.device("cpu"), loader, opt, 1, writer)  # one step
         names = {k.replace("module.", ""): v for k, v in model.named_parameters()}
         out[f"step{s}/loss_rank{rank}"] = np.array([writer.scalars[-1][1]], dtype=np.float64)

@@ -67,6 +67,44 @@ def synthetic_batch(batch_size: int, seed: int):
     return x, t
 
 
+def pool_tie_gap(params, x) -> float:
+    """Smallest gap between the two largest values of any live 2x2 max-pool window (both
+    pooling stages, mnist.py:27,29), computed in float64.  When two candidates are closer than
+    fp32 summation noise, WHICH one max_pool2d's backward routes the gradient to depends on the
+    order in which the convolution summed its 25/500 terms -- the reference's own choice is then
+    arbitrary -- so gradient parity is only defined up to that choice."""
+    pp = {k: v.double() for k, v in params.items()}
+    gaps = []
+    a = x.double()
+    for wn, bn in (("conv1.weight", "conv1.bias"), ("conv2.weight", "conv2.bias")):
+        c = F.relu(F.conv2d(a, pp[wn], pp[bn]))
+        w = c.unfold(2, 2, 2).unfold(3, 2, 2).reshape(*c.shape[:2], c.shape[2] // 2, c.shape[3] // 2, 4)
+        top2 = w.topk(2, dim=-1).values
+        live = top2[..., 0] > 0
+        gaps.append(float((top2[..., 0] - top2[..., 1])[live].min()) if live.any() else 1.0)
+        a = F.max_pool2d(c, 2, 2)
+    return min(gaps)
+
+
+def pool_choice_slack(params, x, idx1, idx2) -> float:
+    """How far (float64) the window candidates picked by the arg-max maps idx1 [B,20,12,12] /
+    idx2 [B,50,4,4] (slot = dy*2+dx) are below the true window maximum, over live windows of
+    both pooling stages.  ~1e-7 means the choice is a valid maximum up to fp32 rounding."""
+    pp = {k: v.double() for k, v in params.items()}
+    a = x.double()
+    worst = 0.0
+    for wn, bn, idx in (("conv1.weight", "conv1.bias", idx1), ("conv2.weight", "conv2.bias", idx2)):
+        c = F.relu(F.conv2d(a, pp[wn], pp[bn]))
+        w = c.unfold(2, 2, 2).unfold(3, 2, 2).reshape(*c.shape[:2], c.shape[2] // 2, c.shape[3] // 2, 4)
+        mx = w.max(dim=-1).values
+        picked = w.gather(-1, torch.as_tensor(idx).long().unsqueeze(-1)).squeeze(-1)
+        live = mx > 1e-6
+        if live.any():
+            worst = max(worst, float((mx - picked)[live].max()))
+        a = F.max_pool2d(c, 2, 2)
+    return worst
+
+
 def forward(params, x: torch.Tensor) -> torch.Tensor:
     """Net.forward (mnist.py:25-33): conv5x5+ReLU, 2x2 max-pool, conv5x5+ReLU,
     2x2 max-pool, flatten to 800, fc+ReLU, fc, log_softmax over the 10 classes."""

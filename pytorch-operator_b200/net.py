@@ -260,14 +260,16 @@ class StepGraph:
     Static input buffers ``x``/``target`` are filled by the caller (e.g. an H2D copy) before
     ``replay()``; ``loss`` is a 0-d view of the device scalar the graph writes."""
 
-    def __init__(self, model: Net, optimizer, batch: int):
+    def __init__(self, model: Net, optimizer, batch: int, x=None, target=None):
         if optimizer.first_step:
             raise RuntimeError("run one eager step first (the first SGD step initialises the momentum buffer)")
         model = getattr(model, "module", model)  # accept our DistributedDataParallel wrapper
         dev = model.device
         self.model, self.optimizer = model, optimizer
-        self.x = torch.zeros(batch, 1, 28, 28, dtype=torch.float32, device=dev)
-        self.target = torch.zeros(batch, dtype=torch.int64, device=dev)
+        # static input buffers (the caller may supply its own, e.g. two views of one packed record)
+        self.x = torch.zeros(batch, 1, 28, 28, dtype=torch.float32, device=dev) if x is None else x
+        self.target = torch.zeros(batch, dtype=torch.int64, device=dev) if target is None else target
+        model._check_inputs(self.x, self.target)
         self.lr, self.momentum = optimizer.lr, optimizer.momentum
         model.workspace(batch)  # allocate outside capture
         self.graph = torch.cuda.CUDAGraph()

@@ -17,10 +17,6 @@ def load_golden(name):
         return {k: z[k] for k in z.files}
 
 
-def batch_seed(step, rank):  # must match oracle/gen_golden.py
-    return 1234 + 97 * step + rank
-
-
 def golden_tensor_check(gold, prefix, name, value, rtol=RTOL, atol_scale=1.0):
     """Compare a full tensor `value` with what the golden file stores under prefix/name
     (whole tensor, or stride sample + sum/l2 for fc1.weight)."""
@@ -49,3 +45,20 @@ def assert_close(a, b, rtol=RTOL, atol_scale=1.0, what=""):
     bad = err > bound
     assert not bad.any(), (f"{what}: {int(bad.sum())}/{a.size} out of tolerance; max err "
                            f"{float(err.max()):.3e} (max|ref| {scale:.3e}, rtol {rtol})")
+
+
+def tie_free_batch(params, B, seed, min_gap=5e-7):
+    """synthetic_batch(B, seed'), with seed' the first seed >= `seed` whose batch has no
+    max-pool near-tie under `params` (oracle.mnist_oracle.pool_tie_gap)."""
+    from oracle import mnist_oracle as mo
+    for s in range(seed, seed + 2000):
+        x, t = mo.synthetic_batch(B, s)
+        if mo.pool_tie_gap(params, x) >= min_gap:
+            return x, t
+    raise AssertionError("no tie-free batch found")
+
+
+def golden_batch(gold, B, step, rank):
+    """The batch gen_golden.py used for (step, rank): the seed is stored in the fixture."""
+    from oracle import mnist_oracle as mo
+    return mo.synthetic_batch(B, int(gold[f"step{step}/seed_rank{rank}"][0]))

@@ -5,7 +5,7 @@ import pytest
 import torch
 
 from oracle import c_oracle, mnist_oracle as mo
-from tests.helpers import NAMES, RTOL, assert_close, batch_seed, golden_tensor_check, load_golden
+from tests.helpers import NAMES, RTOL, assert_close, golden_batch, golden_tensor_check, load_golden
 
 
 def test_param_count_and_init_matches_reference():
@@ -21,7 +21,7 @@ def test_torch_restatement_free_run_matches_reference(case):
     gold = load_golden(case)
     ws, B, nsteps = (int(gold[f"meta/{k}"][0]) for k in ("world_size", "batch_size", "nsteps"))
     params = mo.init_params(1)
-    batches = [[mo.synthetic_batch(B, batch_seed(s, r)) for s in range(nsteps)] for r in range(ws)]
+    batches = [[golden_batch(gold, B, s, r) for s in range(nsteps)] for r in range(ws)]
     trace, _ = mo.train_steps(params, batches)
     # replay again to capture params after each step
     params = mo.init_params(1)
@@ -41,7 +41,7 @@ def test_c_restatement_step0_matches_reference(case):
     gold = load_golden(case)
     B = int(gold["meta/batch_size"][0])
     params = {k: v.numpy() for k, v in mo.init_params(1).items()}
-    x, t = mo.synthetic_batch(B, batch_seed(0, 0))
+    x, t = golden_batch(gold, B, 0, 0)
     loss, logp, grads = c_oracle.loss_and_grads(params, x.numpy(), t.numpy())
     assert abs(loss - float(gold["step0/loss_rank0"][0])) <= RTOL * 2.4
     for n in NAMES:
@@ -53,7 +53,7 @@ def test_c_and_torch_restatements_agree_ws2_average():
     params = {k: v.numpy() for k, v in mo.init_params(1).items()}
     gsum = None
     for r in range(2):
-        x, t = mo.synthetic_batch(64, batch_seed(0, r))
+        x, t = golden_batch(gold, 64, 0, r)
         loss, _, g = c_oracle.loss_and_grads(params, x.numpy(), t.numpy())
         assert abs(loss - float(gold[f"step0/loss_rank{r}"][0])) <= RTOL * 2.4
         gsum = g if gsum is None else {n: gsum[n] + g[n] for n in NAMES}
