@@ -107,6 +107,22 @@ int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, f
 int b200mnist_fc2_logsoftmax_nll(const float *h, const float *w, const float *bias, const int64_t *target, int B,
                                  float *logp, float *loss_out, float *dz2, float *dz1, void *scratch,
                                  void *stream);
+/* No counterpart in the reference: b200mnist_fc2_logsoftmax_nll for callers that cannot supply a
+ * scratch buffer because they may not allocate device memory where they run -- e.g. a plugin
+ * invoked from inside another runtime's callback (cudaMalloc is off limits there: it can
+ * synchronise the whole device), or a process whose device memory is entirely owned by a
+ * foreign pool.  Same arguments and results as b200mnist_fc2_logsoftmax_nll minus `scratch`;
+ * the scratch is a fixed 16,640-byte array inside the library image (resident on every GPU
+ * that loads the library, for the life of the process), hence the limit
+ * B <= B200MNIST_STATIC_MAX_BATCH; larger B returns -10006 with an explanatory message.
+ * The call allocates nothing (no cudaMalloc/cudaFree, no allocating library routine).
+ * The FIRST call on each device looks up the array's device address (a one-time, per-device
+ * set-up that is not stream work): make that first call before starting any stream capture.
+ * All calls on a device share the one array: two calls whose kernels may overlap on the GPU
+ * (different streams, no ordering between them) race on it -- serialise them. */
+#define B200MNIST_STATIC_MAX_BATCH 4096
+int b200mnist_fc2_logsoftmax_nll_static(const float *h, const float *w, const float *bias, const int64_t *target,
+                                        int B, float *logp, float *loss_out, float *dz2, float *dz1, void *stream);
 /* Backward of log_softmax + fc2 for an arbitrary upstream gradient (autograd of mnist.py:32-33
  * when the loss is not the fused NLL): dz2 = dlogp - exp(logp)*sum_j(dlogp), dz1 = (dz2 . W2)*(h>0). */
 int b200mnist_head_bwd(const float *logp, const float *dlogp, const float *h, const float *w, int B, float *dz2,

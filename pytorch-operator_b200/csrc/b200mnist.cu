@@ -388,6 +388,58 @@ int b200mnist_fc2_logsoftmax_nll(const float *h, const float *w, const float *bi
     return launch_head(a, static_cast<cudaStream_t>(stream));
 }
 
+/* ---- allocation-free variant of b200mnist_fc2_logsoftmax_nll ------------------------
+ * Some hosts that embed this library cannot hand it a scratch buffer: a plugin that is
+ * called from inside another runtime's callback is not allowed to call cudaMalloc there
+ * (cudaMalloc may synchronise the whole device, which stalls the runtime's other streams),
+ * and a process whose device memory has been handed in full to someone else's pool has
+ * nothing left to allocate from.  For them the (B + 64)-float scratch of the head kernel
+ * lives in a fixed array inside the library image instead.  Every GPU that loads the library
+ * carries these 16,640 bytes until the process exits, whether the entry point is used or
+ * not, which is why the limit is kept small (B <= B200MNIST_STATIC_MAX_BATCH = 4096). */
+constexpr int kStaticMaxBatch = 4096;
+static __device__ __align__(256) float g_head_scratch[64 + kStaticMaxBatch];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float *g_head_scratch_addr[kMaxDevices] = {};  // device address of g_head_scratch, per device ordinal
+}  // namespace
+
+int b200mnist_fc2_logsoftmax_nll_static(const float *h, const float *w, const float *bias, const int64_t *target,
+                                        int B, float *logp, float *loss_out, float *dz2, float *dz1, void *stream) {
+    if (!h || !w || !bias || !target || !loss_out) return fail_arg(1, "null pointer argument");
+    if (B < 1) return fail_arg(2, "batch size must be at least 1");
+    if (B > kStaticMaxBatch)
+        return fail_arg(6, "batch size exceeds B200MNIST_STATIC_MAX_BATCH (4096): the built-in scratch array is "
+                           "fixed-size; use b200mnist_fc2_logsoftmax_nll with a caller-provided scratch buffer");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
+    if (dev < 0 || dev >= kMaxDevices) return fail_arg(7, "device ordinal out of range for the static scratch table");
+    if (!g_head_scratch_addr[dev]) {
+        // One-time set-up for this device, with this device current.  In host code the name
+        // g_head_scratch is only a handle for the symbol, not an address a kernel can use:
+        // the real per-device address has to be asked for.
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_head_scratch);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaGetSymbolAddress(g_head_scratch)");
+        g_head_scratch_addr[dev] = static_cast<float *>(p);
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    float *scratch = g_head_scratch_addr[dev];
+    // The array keeps whatever the previous call left in it.  Only the ticket word at its head
+    // has to start from zero (the per-row slots are fully rewritten before they are read).
+    e = cudaMemsetAsync(scratch, 0, 256, s);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(static scratch)");
+    HeadArgs a{};
+    a.h_in = h; a.w2 = w; a.b2 = bias; a.target = target; a.logp = logp; a.dz2 = dz2; a.dz1 = dz1;
+    a.ticket = reinterpret_cast<unsigned *>(scratch);
+    a.rows = scratch + 64;
+    a.stats_out = loss_out;
+    a.B = B; a.nsplit = 0; a.want_correct = 0; a.inv_B = 1.0f / (float)B; a.loss_scale = 1.0f / (float)B;
+    return launch_head(a, s);
+}
+
 int b200mnist_head_bwd(const float *logp, const float *dlogp, const float *h, const float *w, int B, float *dz2,
                        float *dz1, void *stream) {
     if (!logp || !dlogp || !h || !w || !dz2 || !dz1) return fail_arg(1, "null pointer argument");
