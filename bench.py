@@ -40,11 +40,8 @@ KERNEL_WORK = {
     "conv2_relu_pool_fwd": (1_600_000, 11520 + 3200 + 800, 100_200),
     "fc1 forward gemm": (400_000, 3200 + 2000, 1_602_000),
     "fc2/log_softmax/nll head": (10_000, 2000 + 2000 + 80 + 8, 20_040),
-    "fc2 wgrad": (5_000, 2000 + 40, 20_040),
-    "fc1 wgrad gemm": (400_000, 2000 + 3200, 1_602_000),
-    "fc1 dgrad gemm": (400_000, 2000 + 3200, 1_600_000),
-    "conv2 dgrad": (1_600_000, 3200 + 800 + 3200 + 11520, 100_000),
-    "conv2 wgrad": (1_600_000, 3200 + 800 + 3200 + 11520, 100_200),
+    "fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)": (805_000, 2000 * 2 + 3200 + 3200 + 2000 + 40, 3_220_000),
+    "conv2 backward (wgrad + dgrad)": (3_200_000, 3200 + 3200 + 800 + 11520 + 11520, 200_200),
     "conv1 wgrad": (288_000, 3136 + 11520 + 11520 + 2880, 2080),
     "sgd momentum": (0, 0, 5 * PARAM_BYTES),
     "grad finalize": (0, 0, 2 * 31_080 * 4),

@@ -79,8 +79,8 @@ Plan make_plan(int B) {
     p.fc2w_rows = ceil_div(B, p.fc2w_split);
     p.fc2w_split = ceil_div(B, p.fc2w_rows);
     p.c2w_split = clampi(ceil_div(B, 2), 1, 29);
-    p.c1w_split = clampi(B, 1, 148);
-    p.c2dg_gx = clampi(B, 1, 88);
+    p.c1w_split = clampi(B, 1, kMaxGradSplit);
+    p.c2dg_gx = clampi(B, 1, 60);
     return p;
 }
 
@@ -119,7 +119,7 @@ Workspace carve(void *base, int B) {
     w.dp2_part = static_cast<float *>(take(8 * Bz * kP2Elems * 4));
     w.fc2w_part = static_cast<float *>(take((size_t)32 * kFc2PartStride * 4));
     w.c2w_part = static_cast<float *>(take((size_t)29 * kC2PartStride * 4));
-    w.c1w_part = static_cast<float *>(take((size_t)148 * kC1PartStride * 4));
+    w.c1w_part = static_cast<float *>(take((size_t)kMaxGradSplit * kC1PartStride * 4));
     w.bytes = off;
     return w;
 }
@@ -169,19 +169,22 @@ int launch_head(const HeadArgs &a, cudaStream_t s) {
 }
 int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
                   float *gw1, float *gb1, float *dp2_part, float *fc2w_part, const Plan &pl, cudaStream_t s) {
-    fc2_wgrad_kernel<<<dim3(ceil_div(500, kFc2wThreads), pl.fc2w_split), kFc2wThreads, 0, s>>>(dz2, h, fc2w_part, B,
-                                                                                               pl.fc2w_rows);
-    CHECK_LAUNCH("fc2 wgrad", s);
-    GemmArgs g{};  // gW1[n,k] = sum_b dz1[b,n] p2[b,k] ; gb1[n] = sum_b dz1[b,n]
+    FcBwdArgs a{};
+    GemmArgs &g = a.wg;  // gW1[n,k] = sum_b dz1[b,n] p2[b,k] ; gb1[n] = sum_b dz1[b,n]
     g.A = dz1; g.B = p2; g.C = gw1; g.rowsum = gb1;
     g.M = 500; g.N = 800; g.K = B; g.lda = 500; g.ldb = 800; g.ldc = 800; g.kchunk = B;
-    gemm_kernel<64, 64, 4, 4, false, false><<<dim3(ceil_div(800, 64), ceil_div(500, 64), 1), 256, 0, s>>>(g);
-    CHECK_LAUNCH("fc1 wgrad gemm", s);
-    GemmArgs d{};  // dp2[b,k] = sum_n dz1[b,n] W1[n,k]
+    a.wg_gx = ceil_div(800, 64);
+    a.wg_n = a.wg_gx * ceil_div(500, 64);
+    GemmArgs &d = a.dg;  // dp2[b,k] = sum_n dz1[b,n] W1[n,k]
     d.A = dz1; d.B = w1; d.C = dp2_part;
     d.M = B; d.N = 800; d.K = 500; d.lda = 500; d.ldb = 800; d.ldc = 800; d.kchunk = pl.dg_kchunk;
-    gemm_kernel<64, 32, 4, 2, true, false><<<dim3(ceil_div(800, 32), ceil_div(B, 64), pl.dg_split), 256, 0, s>>>(d);
-    CHECK_LAUNCH("fc1 dgrad gemm", s);
+    a.dg_gx = ceil_div(800, 32);
+    a.dg_gy = ceil_div(B, 64);
+    a.dg_n = a.dg_gx * a.dg_gy * pl.dg_split;
+    a.dz2 = dz2; a.h = h; a.fc2_part = fc2w_part; a.B = B; a.fc2_rows = pl.fc2w_rows;
+    a.fc2_gx = ceil_div(500, kFc2wThreads);
+    fc_bwd_kernel<<<a.wg_n + a.dg_n + a.fc2_gx * pl.fc2w_split, 256, 0, s>>>(a);
+    CHECK_LAUNCH("fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)", s);
     return 0;
 }
 int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const float *p2, const uint8_t *i2,
@@ -189,22 +192,22 @@ int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const fl
                      cudaStream_t s) {
     static bool attr_done = false;  // per process; setting it again is harmless
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             kDgSmemBytes);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(conv2_dgrad)");
+        cudaError_t e = cudaFuncSetAttribute(conv2_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             kConv2BwdSmemBytes);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(conv2_bwd)");
         attr_done = true;
     }
-    conv2_dgrad_kernel<<<dim3(pl.c2dg_gx, 20 / kDgIcPerCta), kDgThreads, kDgSmemBytes, s>>>(dp2, nsplit, split_stride,
-                                                                                            p2, i2, w, dp1, B);
-    CHECK_LAUNCH("conv2 dgrad", s);
-    conv2_wgrad_kernel<<<dim3(20 / kWgIcPerCta, pl.c2w_split), kWgThreads, 0, s>>>(dp2, nsplit, split_stride, p2, i2,
-                                                                                   p1, c2w_part, B);
-    CHECK_LAUNCH("conv2 wgrad", s);
+    Conv2BwdArgs a{};
+    a.dp2 = dp2; a.p2 = p2; a.p1 = p1; a.w = w; a.i2 = i2; a.dp1 = dp1; a.part = c2w_part;
+    a.split_stride = split_stride; a.nsplit = nsplit; a.B = B;
+    a.wg_gy = pl.c2w_split; a.n_wg = 5 * pl.c2w_split; a.dg_gx = pl.c2dg_gx;
+    conv2_bwd_kernel<<<a.n_wg + 5 * a.dg_gx, kConvBwdThreads, kConv2BwdSmemBytes, s>>>(a);
+    CHECK_LAUNCH("conv2 backward (wgrad + dgrad)", s);
     return 0;
 }
 int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
                      const Plan &pl, cudaStream_t s) {
-    conv1_wgrad_kernel<<<pl.c1w_split, kC1wThreads, 0, s>>>(x, dp1, p1, i1, c1w_part, B);
+    conv1_wgrad_kernel<<<dim3(pl.c1w_split, 2), kC1wThreads, 0, s>>>(x, dp1, p1, i1, c1w_part, B);
     CHECK_LAUNCH("conv1 wgrad", s);
     return 0;
 }
@@ -445,7 +448,7 @@ int b200mnist_head_bwd(const float *logp, const float *dlogp, const float *h, co
     if (!logp || !dlogp || !h || !w || !dz2 || !dz1) return fail_arg(1, "null pointer argument");
     if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    head_bwd_kernel<<<B, kHeadThreads, 0, s>>>(logp, dlogp, h, w, dz2, dz1);
+    head_bwd_kernel<<<B, 128, 0, s>>>(logp, dlogp, h, w, dz2, dz1);
     CHECK_LAUNCH("head backward", s);
     return 0;
 }
@@ -489,7 +492,7 @@ int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, 
            reduce_to(gb, 50, part + 25024, pl.c2w_split, kC2PartStride, s);
 }
 
-int64_t b200mnist_conv1_bwd_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)148 * kC1PartStride * 4; }
+int64_t b200mnist_conv1_bwd_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)kMaxGradSplit * kC1PartStride * 4; }
 
 int b200mnist_conv1_bwd(const float *dp1, const float *p1, const uint8_t *idx1, const float *x, int B, float *gw,
                         float *gb, void *scratch, void *stream) {

@@ -21,6 +21,22 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// Sum of up to MAX partial values p[0], p[stride], ..., in a fixed order.  All MAX loads are
+// issued before the first add (a serial "v += p[s*stride]" walk costs one full memory latency
+// per partial: at 8-148 partials that dominated the v1 step).  Missing partials read as +0,
+// which leaves the sum bit-identical.
+template <int MAX>
+__device__ __forceinline__ float sum_partials(const float *p, int nsplit, size_t stride) {
+    float v[MAX];
+#pragma unroll
+    for (int s = 0; s < MAX; ++s) v[s] = (s < nsplit) ? __ldcg(p + (size_t)s * stride) : 0.f;
+    float acc = v[0];
+#pragma unroll
+    for (int s = 1; s < MAX; ++s) acc += v[s];
+    return acc;
+}
+constexpr int kMaxGradSplit = 32;  // upper bound of every batch-split weight-gradient kernel
+
 // One gradient tensor whose value is the sum of `nsplit` partial buffers
 // (part + s*stride, s < nsplit), landing at flat offset `off` .. off+n.
 struct GradSegment {

@@ -5,21 +5,38 @@
 
 namespace b200mnist {
 
+constexpr int kMaxDgSplit = 8;  // fc1 data-gradient split-K upper bound (dp2 partials)
+
 // Gradient w.r.t. the conv2 output map of one image, built in shared memory from the
 // gradient of the pooled map: max-pool backward routes each value to the arg-max slot of
 // its 2x2 window, ReLU backward kills it where the (post-ReLU) maximum was 0.
 //   D_s : [50][ld] floats, already zero-filled; dp2 may be the sum of `nsplit` partials.
+// All global loads of a thread (<= 4 elements x (nsplit + 2)) are issued before any is used.
+template <int NTHREADS>
 __device__ __forceinline__ void scatter_dconv2(float *D_s, int ld, const float *__restrict__ dp2, int nsplit,
                                                size_t split_stride, const float *__restrict__ p2,
-                                               const uint8_t *__restrict__ i2, size_t b, int tid, int nthreads) {
-    for (int e = tid; e < kP2Elems; e += nthreads) {
-        const size_t o = b * kP2Elems + e;
-        float g = dp2[o];
-        for (int s = 1; s < nsplit; ++s) g += dp2[s * split_stride + o];
-        if (p2[o] > 0.f) {
-            const int oc = e >> 4, p = e & 15, q = i2[o];
-            const int oy = 2 * (p >> 2) + (q >> 1), ox = 2 * (p & 3) + (q & 1);
-            D_s[oc * ld + oy * 8 + ox] = g;
+                                               const uint8_t *__restrict__ i2, size_t b, int tid) {
+    constexpr int PER = (kP2Elems + NTHREADS - 1) / NTHREADS;
+    float g[PER], pv[PER];
+    int q[PER];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        const int e = tid + j * NTHREADS;
+        g[j] = 0.f; pv[j] = 0.f; q[j] = 0;
+        if (e < kP2Elems) {
+            const size_t o = b * kP2Elems + e;
+            pv[j] = __ldcg(p2 + o);
+            q[j] = i2[o];
+            g[j] = sum_partials<kMaxDgSplit>(dp2 + o, nsplit, split_stride);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        const int e = tid + j * NTHREADS;
+        if (e < kP2Elems && pv[j] > 0.f) {
+            const int oc = e >> 4, p = e & 15;
+            const int oy = 2 * (p >> 2) + (q[j] >> 1), ox = 2 * (p & 3) + (q[j] & 1);
+            D_s[oc * ld + oy * 8 + ox] = g[j];
         }
     }
 }
@@ -34,29 +51,43 @@ __device__ __forceinline__ void scatter_dconv2(float *D_s, int ld, const float *
 // images the CTA loops over.
 // ---------------------------------------------------------------------------------
 constexpr int kDgIcPerCta = 4;
-constexpr int kDgThreads = 256;
+constexpr int kConvBwdThreads = 256;
 constexpr int kDgLdT = 68;
-constexpr int kDgSmemBytes = (50 * 100 + 50 * 64 + 100 * kDgLdT) * 4;  // 60,000 B (dynamic)
+constexpr int kDgSmemFloats = 50 * 100 + 50 * 64 + 100 * kDgLdT;  // 15,000 floats = 60,000 B
 
-__global__ void __launch_bounds__(kDgThreads)
-conv2_dgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_stride, const float *__restrict__ p2,
-                   const uint8_t *__restrict__ i2, const float *__restrict__ w, float *__restrict__ dp1, int B) {
-    extern __shared__ __align__(16) float smem[];
+__device__ __forceinline__ void conv2_dgrad_tile(float *smem, const float *__restrict__ dp2, int nsplit,
+                                                 size_t split_stride, const float *__restrict__ p2,
+                                                 const uint8_t *__restrict__ i2, const float *__restrict__ w,
+                                                 float *__restrict__ dp1, int B, int vx, int gx, int vy) {
     float *W_s = smem;                // [50 oc][100 m]
     float *D_s = W_s + 50 * 100;      // [50 oc][64 n]
     float *T_s = D_s + 50 * 64;       // [100 m][68]
-    const int tid = threadIdx.x, ic0 = blockIdx.y * kDgIcPerCta;
-    for (int i = tid; i < 50 * 25; i += kDgThreads) {
-        const int oc = i / 25, m4 = (i % 25) * 4;
-        *reinterpret_cast<float4 *>(&W_s[oc * 100 + m4]) =
-            __ldg(reinterpret_cast<const float4 *>(w + (size_t)oc * 500 + ic0 * 25 + m4));
+    const int tid = threadIdx.x, ic0 = vy * kDgIcPerCta;
+    {
+        float4 wv[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const int i = tid + j * kConvBwdThreads;
+            if (i < 50 * 25) {
+                const int oc = i / 25, m4 = (i % 25) * 4;
+                wv[j] = __ldg(reinterpret_cast<const float4 *>(w + (size_t)oc * 500 + ic0 * 25 + m4));
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const int i = tid + j * kConvBwdThreads;
+            if (i < 50 * 25) {
+                const int oc = i / 25, m4 = (i % 25) * 4;
+                *reinterpret_cast<float4 *>(&W_s[oc * 100 + m4]) = wv[j];
+            }
+        }
     }
     const int tm = tid >> 3, tn = tid & 7;  // tm < 25 active: rows 4*tm..+3; cols 4*tn..+3 and 32+4*tn..+3
-    for (int b = blockIdx.x; b < B; b += gridDim.x) {
-        for (int i = tid; i < 50 * 64 / 4; i += kDgThreads)
+    for (int b = vx; b < B; b += gx) {
+        for (int i = tid; i < 50 * 64 / 4; i += kConvBwdThreads)
             reinterpret_cast<float4 *>(D_s)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncthreads();  // also orders W_s (first trip) and the previous trip's T_s readers
-        scatter_dconv2(D_s, 64, dp2, nsplit, split_stride, p2, i2, (size_t)b, tid, kDgThreads);
+        scatter_dconv2<kConvBwdThreads>(D_s, 64, dp2, nsplit, split_stride, p2, i2, (size_t)b, tid);
         __syncthreads();
         if (tm < 25) {
             float acc[4][8];
@@ -85,7 +116,7 @@ conv2_dgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_strid
             }
         }
         __syncthreads();
-        for (int o = tid; o < kDgIcPerCta * 144; o += kDgThreads) {
+        for (int o = tid; o < kDgIcPerCta * 144; o += kConvBwdThreads) {
             const int icl = o / 144, r = o - icl * 144, y = r / 12, x = r - y * 12;
             float s = 0.f;
 #pragma unroll
@@ -115,17 +146,18 @@ conv2_dgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_strid
 // batch slices are summed in a fixed order by grad_finalize / the fused SGD kernel.
 // ---------------------------------------------------------------------------------
 constexpr int kWgIcPerCta = 4;
-constexpr int kWgThreads = 256;
 constexpr int kWgLdD = 68;
 constexpr int kC2PartStride = 25088;  // 25,000 weights @0, 50 biases @25,024
+constexpr int kWgSmemFloats = 2 * kWgIcPerCta * 144 + 2 * 50 * kWgLdD;  // 7,952 floats
 
-__global__ void __launch_bounds__(kWgThreads)
-conv2_wgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_stride, const float *__restrict__ p2,
-                   const uint8_t *__restrict__ i2, const float *__restrict__ p1, float *__restrict__ part, int B) {
-    __shared__ __align__(16) float P_s[2][kWgIcPerCta * 144];  //  4,608 B
-    __shared__ __align__(16) float D_s[2][50 * kWgLdD];        // 27,200 B (later: the 50 x 100 output tile)
+__device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__restrict__ dp2, int nsplit,
+                                                 size_t split_stride, const float *__restrict__ p2,
+                                                 const uint8_t *__restrict__ i2, const float *__restrict__ p1,
+                                                 float *__restrict__ part, int B, int vx, int vy, int gy) {
+    float *P_s = smem;                                // [2][4 ic][144]
+    float *D_s = smem + 2 * kWgIcPerCta * 144;        // [2][50][68]   (later: the 50 x 100 output tile)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, icl = warp & 3, par = warp >> 2;
-    const int ic0 = blockIdx.x * kWgIcPerCta;
+    const int ic0 = vx * kWgIcPerCta;
     const bool active = lane < 25;
     float acc0[5][5], acc1[5][5], accb0 = 0.f, accb1 = 0.f;
 #pragma unroll
@@ -133,25 +165,37 @@ conv2_wgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_strid
 #pragma unroll
         for (int j = 0; j < 5; ++j) acc0[i][j] = acc1[i][j] = 0.f;
 
-    for (int bb = blockIdx.y * 2; bb < B; bb += gridDim.y * 2) {
+    for (int bb = vy * 2; bb < B; bb += gy * 2) {
         __syncthreads();  // previous trip's readers are done
-        for (int i = tid; i < 2 * 50 * kWgLdD / 4; i += kWgThreads)
-            reinterpret_cast<float4 *>(&D_s[0][0])[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int i = tid; i < 2 * kWgIcPerCta * 36; i += kWgThreads) {
-            const int pr = i / (kWgIcPerCta * 36), r = i - pr * (kWgIcPerCta * 36), b = bb + pr;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (b < B) v = __ldg(reinterpret_cast<const float4 *>(p1 + (size_t)b * kP1Elems + ic0 * 144) + r);
-            reinterpret_cast<float4 *>(&P_s[pr][0])[r] = v;
+        {   // stage the two p1 tiles (global load first, so it overlaps the zero-fill below)
+            float4 pv[2];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int i = tid + j * kConvBwdThreads;
+                pv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i < 2 * kWgIcPerCta * 36) {
+                    const int pr = i / (kWgIcPerCta * 36), r = i - pr * (kWgIcPerCta * 36), b = bb + pr;
+                    if (b < B) pv[j] = __ldg(reinterpret_cast<const float4 *>(p1 + (size_t)b * kP1Elems + ic0 * 144) + r);
+                }
+            }
+            for (int i = tid; i < 2 * 50 * kWgLdD / 4; i += kConvBwdThreads)
+                reinterpret_cast<float4 *>(D_s)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int i = tid + j * kConvBwdThreads;
+                if (i < 2 * kWgIcPerCta * 36) reinterpret_cast<float4 *>(P_s)[i] = pv[j];
+            }
         }
         __syncthreads();
-        scatter_dconv2(&D_s[0][0], kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb, tid, kWgThreads);
+        scatter_dconv2<kConvBwdThreads>(D_s, kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb, tid);
         if (bb + 1 < B)
-            scatter_dconv2(&D_s[1][0], kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb + 1, tid, kWgThreads);
+            scatter_dconv2<kConvBwdThreads>(D_s + 50 * kWgLdD, kWgLdD, dp2, nsplit, split_stride, p2, i2,
+                                            (size_t)bb + 1, tid);
         __syncthreads();
         if (active && bb + par < B) {
-            const float *ps = &P_s[par][icl * 144];
-            const float *d0p = &D_s[par][lane * kWgLdD];
-            const float *d1p = &D_s[par][(lane + 25) * kWgLdD];
+            const float *ps = P_s + (par * kWgIcPerCta + icl) * 144;
+            const float *d0p = D_s + par * 50 * kWgLdD + lane * kWgLdD;
+            const float *d1p = d0p + 25 * kWgLdD;
 #pragma unroll 1
             for (int oy = 0; oy < 8; ++oy) {
                 float strip[5][12];
@@ -185,7 +229,7 @@ conv2_wgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_strid
     }
     // ---- combine the two image-parity halves, then write the 50 x 100 tile coalesced ----
     __syncthreads();
-    float *O_s = &D_s[0][0];  // [50 oc][100]  (+ 64 bias slots at 5000)
+    float *O_s = D_s;  // [50 oc][100]  (+ 64 bias slots at 5000)
     if (par == 1 && active) {
 #pragma unroll
         for (int ky = 0; ky < 5; ++ky)
@@ -208,52 +252,87 @@ conv2_wgrad_kernel(const float *__restrict__ dp2, int nsplit, size_t split_strid
         if (icl == 0) { O_s[5000 + lane] += accb0; O_s[5000 + lane + 25] += accb1; }
     }
     __syncthreads();
-    float *po = part + (size_t)blockIdx.y * kC2PartStride;
-    for (int i = tid; i < 5000; i += kWgThreads) {
+    float *po = part + (size_t)vy * kC2PartStride;
+    for (int i = tid; i < 5000; i += kConvBwdThreads) {
         const int oc = i / 100, m = i - oc * 100;
         po[oc * 500 + ic0 * 25 + m] = O_s[i];
     }
-    if (blockIdx.x == 0 && tid < 50) po[25024 + tid] = O_s[5000 + tid];
+    if (vx == 0 && tid < 50) po[25024 + tid] = O_s[5000 + tid];
+}
+
+// One launch for both halves of the conv2 backward (they only share their inputs):
+// CTAs [0, n_wg) are weight-gradient tiles (5 channel tiles x wg_gy batch slices), the rest
+// data-gradient tiles (dg_gx image slots x 5 channel tiles).  The weight-gradient CTAs come
+// first because they are the longer ones.
+struct Conv2BwdArgs {
+    const float *dp2, *p2, *p1, *w;
+    const uint8_t *i2;
+    float *dp1, *part;
+    size_t split_stride;
+    int nsplit, B, wg_gy, n_wg, dg_gx;
+};
+constexpr int kConv2BwdSmemBytes = kDgSmemFloats * 4;  // 60,000 B dynamic (covers both roles)
+
+__global__ void __launch_bounds__(kConvBwdThreads) conv2_bwd_kernel(const Conv2BwdArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    int b = blockIdx.x;
+    if (b < a.n_wg) {
+        conv2_wgrad_tile(smem, a.dp2, a.nsplit, a.split_stride, a.p2, a.i2, a.p1, a.part, a.B, b % 5, b / 5, a.wg_gy);
+    } else {
+        b -= a.n_wg;
+        conv2_dgrad_tile(smem, a.dp2, a.nsplit, a.split_stride, a.p2, a.i2, a.w, a.dp1, a.B, b % a.dg_gx, a.dg_gx,
+                         b / a.dg_gx);
+    }
 }
 
 // ---------------------------------------------------------------------------------
 // conv1 weight/bias gradient (the input image needs no gradient).  The conv1 output
 // gradient has one non-zero per 2x2 window (pool arg-max) and none where ReLU was inactive,
 // so the sum is taken sparsely: warp = channel, lane = filter tap (25 active, lane 25 sums
-// the bias gradient); per window the gradient value and arg-max slot are fetched 32 at a
-// time and broadcast with shuffles, and windows with a zero gradient are skipped.
-// blockIdx.x slices the batch; each CTA writes a partial [512 + 64].
+// the bias gradient).  A lane first fetches the gradient / arg-max of its share of the 144
+// windows (5 independent loads each of p1, dp1, idx), then the values are broadcast with
+// shuffles and windows with a zero gradient are skipped.  grid = (batch slices, 2 channel
+// halves); each CTA writes a partial [512 + 64] (its half of the channels).
 // ---------------------------------------------------------------------------------
-constexpr int kC1wThreads = 640;
+constexpr int kC1wThreads = 320;    // 10 channels x 32 lanes
 constexpr int kC1PartStride = 576;  // 500 weights @0, 20 biases @512
 
 __global__ void __launch_bounds__(kC1wThreads)
 conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
                    const uint8_t *__restrict__ i1, float *__restrict__ part, int B) {
     __shared__ __align__(16) float xs[kXElems];
-    const int tid = threadIdx.x, c = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, c = blockIdx.y * 10 + (tid >> 5), lane = tid & 31;
     const int ky = lane / 5, kx = lane - ky * 5;  // lanes >= 25: unused taps
     float acc = 0.f;
     for (int b = blockIdx.x; b < B; b += gridDim.x) {
-        __syncthreads();
-        for (int i = tid; i < kXElems / 4; i += kC1wThreads)
-            reinterpret_cast<float4 *>(xs)[i] = __ldg(reinterpret_cast<const float4 *>(x + (size_t)b * kXElems) + i);
-        __syncthreads();
         const size_t base = ((size_t)b * 20 + c) * 144;
-        for (int w0 = 0; w0 < 144; w0 += 32) {
-            const int wl = w0 + lane;
-            float gl = 0.f;
-            int ol = 0;
+        float gl[5];
+        int ol[5];
+        float4 xv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tid < kXElems / 4) xv = __ldg(reinterpret_cast<const float4 *>(x + (size_t)b * kXElems) + tid);
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const int wl = j * 32 + lane;
+            gl[j] = 0.f;
+            ol[j] = 0;
             if (wl < 144) {
-                const float pv = p1[base + wl];
-                if (pv > 0.f) gl = dp1[base + wl];
+                const float pv = __ldcg(p1 + base + wl);
+                const float gv = __ldcg(dp1 + base + wl);
                 const int q = i1[base + wl];
-                ol = (2 * (wl / 12) + (q >> 1)) * 28 + 2 * (wl % 12) + (q & 1);
+                gl[j] = pv > 0.f ? gv : 0.f;
+                ol[j] = (2 * (wl / 12) + (q >> 1)) * 28 + 2 * (wl % 12) + (q & 1);
             }
-            const int cnt = min(32, 144 - w0);
-            for (int j = 0; j < cnt; ++j) {
-                const float g = __shfl_sync(0xffffffffu, gl, j);
-                const int o = __shfl_sync(0xffffffffu, ol, j);
+        }
+        __syncthreads();  // previous image's readers of xs are done
+        if (tid < kXElems / 4) reinterpret_cast<float4 *>(xs)[tid] = xv;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const int cnt = j < 4 ? 32 : 16;
+#pragma unroll 4
+            for (int l = 0; l < cnt; ++l) {
+                const float g = __shfl_sync(0xffffffffu, gl[j], l);
+                const int o = __shfl_sync(0xffffffffu, ol[j], l);
                 if (g != 0.f) {
                     if (lane < 25) acc = fmaf(g, xs[o + ky * 28 + kx], acc);
                     else if (lane == 25) acc += g;

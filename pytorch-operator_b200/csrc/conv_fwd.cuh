@@ -124,15 +124,43 @@ conv2_relu_pool_fwd_kernel(const float *__restrict__ in, const float *__restrict
     __shared__ __align__(16) float in_s[kC2ImgPerCta * kP1Elems];  // 23,040 B; later the 4x40x32 reduce buffer
     __shared__ __align__(16) float w_s[500 * 12];                  // 24,000 B
     const int t = threadIdx.x, b0 = blockIdx.x * kC2ImgPerCta, oc0 = blockIdx.y * kC2OcPerCta;
-    for (int i = t; i < kC2ImgPerCta * kP1Elems / 4; i += kC2Threads) {
-        const int img = i / (kP1Elems / 4), b = b0 + img;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (b < B) v = __ldg(reinterpret_cast<const float4 *>(in + (size_t)b * kP1Elems) + (i - img * (kP1Elems / 4)));
-        reinterpret_cast<float4 *>(in_s)[i] = v;
-    }
-    for (int e = t; e < kC2OcPerCta * 500; e += kC2Threads) {
-        const int oc = e / 500, r = e - oc * 500;
-        w_s[r * 12 + oc] = __ldg(w + (size_t)(oc0 + oc) * 500 + r);
+    {   // stage both operands with every global load in flight before the first store
+        constexpr int kImgVec = kC2ImgPerCta * kP1Elems / 4;        // 1440 float4
+        constexpr int kWVec = kC2OcPerCta * 500 / 4;                // 1250 float4 (10 contiguous rows of W)
+        constexpr int kImgPer = (kImgVec + kC2Threads - 1) / kC2Threads, kWPer = (kWVec + kC2Threads - 1) / kC2Threads;
+        float4 iv[kImgPer], wv[kWPer];
+#pragma unroll
+        for (int j = 0; j < kImgPer; ++j) {
+            const int i = t + j * kC2Threads;
+            iv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i < kImgVec) {
+                const int img = i / (kP1Elems / 4), b = b0 + img;
+                if (b < B) iv[j] = __ldg(reinterpret_cast<const float4 *>(in + (size_t)b * kP1Elems) + (i - img * (kP1Elems / 4)));
+            }
+        }
+        const float4 *wg = reinterpret_cast<const float4 *>(w + (size_t)oc0 * 500);
+#pragma unroll
+        for (int j = 0; j < kWPer; ++j) {
+            const int i = t + j * kC2Threads;
+            wv[j] = i < kWVec ? __ldg(wg + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int j = 0; j < kImgPer; ++j) {
+            const int i = t + j * kC2Threads;
+            if (i < kImgVec) reinterpret_cast<float4 *>(in_s)[i] = iv[j];
+        }
+#pragma unroll
+        for (int j = 0; j < kWPer; ++j) {
+            const int i = t + j * kC2Threads;
+            if (i < kWVec) {  // element e = 4*i of the [10][500] block -> w_s[(ic*25+k)][oc]
+                const float v[4] = {wv[j].x, wv[j].y, wv[j].z, wv[j].w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int e = 4 * i + u, oc = e / 500, r = e - oc * 500;
+                    w_s[r * 12 + oc] = v[u];
+                }
+            }
+        }
     }
     __syncthreads();
     const int warp = t >> 5, lane = t & 31, img = lane >> 4, pos = lane & 15, py = pos >> 2, px = pos & 3;

@@ -9,7 +9,8 @@ namespace b200mnist {
 // fp32 SIMT GEMM  C[M,N] = sum_k A(m,k) * B(k,n), shared-memory tiled, register blocked,
 // optional split-K across blockIdx.z (partials are reduced by the consumer kernel, so
 // a split costs no extra launch).  fp32 FMA keeps the 1e-5 parity bound that a single
-// TF32 pass (10-bit mantissa) cannot.
+// TF32 pass (10-bit mantissa) cannot.  The next k-tile is fetched into registers while
+// the current one is multiplied (one exposed global latency per CTA, not one per tile).
 //   A_KCONTIG : A(m,k) = A[m*lda + k]  (else A[k*lda + m])
 //   B_KCONTIG : B(k,n) = B[n*ldb + k]  (else B[k*ldb + n])
 // Requirements: leading dimensions and the contiguous extents are multiples of 4,
@@ -26,15 +27,59 @@ struct GemmArgs {
     int M, N, K, lda, ldb, ldc, kchunk, relu;
 };
 
+template <int ROWS, int NT, bool KCONTIG>
+struct TileLoader {
+    // One operand tile of ROWS (m or n) x kGemmBK (k) floats, moved as float4.
+    static constexpr int kVec = ROWS * kGemmBK / 4;
+    static constexpr int kPerThread = (kVec + NT - 1) / NT;
+    float4 r[kPerThread];
+
+    __device__ __forceinline__ void load(const float *base, int ld, int row0, int nrows, int k0, int kend, int tid) {
+#pragma unroll
+        for (int j = 0; j < kPerThread; ++j) {
+            const int i = tid + j * NT;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i < kVec) {
+                if (KCONTIG) {
+                    const int row = i / (kGemmBK / 4), k4 = (i % (kGemmBK / 4)) * 4;
+                    if (row0 + row < nrows && k0 + k4 < kend)
+                        v = __ldg(reinterpret_cast<const float4 *>(base + (size_t)(row0 + row) * ld + k0 + k4));
+                } else {
+                    const int k = i / (ROWS / 4), r4 = (i % (ROWS / 4)) * 4;
+                    if (k0 + k < kend && row0 + r4 < nrows)
+                        v = __ldg(reinterpret_cast<const float4 *>(base + (size_t)(k0 + k) * ld + row0 + r4));
+                }
+            }
+            r[j] = v;
+        }
+    }
+    __device__ __forceinline__ void store(float *S, int lds, int tid) const {  // S[k][row], row stride lds
+#pragma unroll
+        for (int j = 0; j < kPerThread; ++j) {
+            const int i = tid + j * NT;
+            if (i < kVec) {
+                if (KCONTIG) {
+                    const int row = i / (kGemmBK / 4), k4 = (i % (kGemmBK / 4)) * 4;
+                    S[(k4 + 0) * lds + row] = r[j].x;
+                    S[(k4 + 1) * lds + row] = r[j].y;
+                    S[(k4 + 2) * lds + row] = r[j].z;
+                    S[(k4 + 3) * lds + row] = r[j].w;
+                } else {
+                    const int k = i / (ROWS / 4), r4 = (i % (ROWS / 4)) * 4;
+                    *reinterpret_cast<float4 *>(&S[k * lds + r4]) = r[j];
+                }
+            }
+        }
+    }
+};
+
 template <int BM, int BN, int TM, int TN, bool A_KCONTIG, bool B_KCONTIG>
-__global__ void __launch_bounds__((BM / TM) * (BN / TN)) gemm_kernel(const GemmArgs g) {
+__device__ __forceinline__ void gemm_tile(const GemmArgs &g, int bx, int by, int bz, float *As, float *Bs) {
     constexpr int NT = (BM / TM) * (BN / TN);
     constexpr int LDA_S = BM + 4, LDB_S = BN + 4;
-    __shared__ __align__(16) float As[kGemmBK * LDA_S];
-    __shared__ __align__(16) float Bs[kGemmBK * LDB_S];
     const int tid = threadIdx.x, tx = tid % (BN / TN), ty = tid / (BN / TN);
-    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-    const int kbeg = blockIdx.z * g.kchunk, kend = min(g.K, kbeg + g.kchunk);
+    const int m0 = by * BM, n0 = bx * BN;
+    const int kbeg = bz * g.kchunk, kend = min(g.K, kbeg + g.kchunk);
     float acc[TM][TN];
     float rs[TM];
 #pragma unroll
@@ -43,69 +88,49 @@ __global__ void __launch_bounds__((BM / TM) * (BN / TN)) gemm_kernel(const GemmA
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
     }
-    const bool want_rs = (g.rowsum != nullptr) && blockIdx.x == 0 && tx == 0;
-
-    for (int k0 = kbeg; k0 < kend; k0 += kGemmBK) {
-        // ---- stage A tile (BM x BK) as As[k][m] ----
-        if (A_KCONTIG) {
-            for (int i = tid; i < BM * (kGemmBK / 4); i += NT) {
-                const int m = i / (kGemmBK / 4), k4 = (i % (kGemmBK / 4)) * 4;
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (m0 + m < g.M && k0 + k4 < kend)
-                    v = __ldg(reinterpret_cast<const float4 *>(g.A + (size_t)(m0 + m) * g.lda + k0 + k4));
-                As[(k4 + 0) * LDA_S + m] = v.x;
-                As[(k4 + 1) * LDA_S + m] = v.y;
-                As[(k4 + 2) * LDA_S + m] = v.z;
-                As[(k4 + 3) * LDA_S + m] = v.w;
-            }
-        } else {
-            for (int i = tid; i < kGemmBK * (BM / 4); i += NT) {
-                const int k = i / (BM / 4), m4 = (i % (BM / 4)) * 4;
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (k0 + k < kend && m0 + m4 < g.M)
-                    v = __ldg(reinterpret_cast<const float4 *>(g.A + (size_t)(k0 + k) * g.lda + m0 + m4));
-                *reinterpret_cast<float4 *>(&As[k * LDA_S + m4]) = v;
-            }
-        }
-        // ---- stage B tile (BK x BN) as Bs[k][n] ----
-        if (B_KCONTIG) {
-            for (int i = tid; i < BN * (kGemmBK / 4); i += NT) {
-                const int n = i / (kGemmBK / 4), k4 = (i % (kGemmBK / 4)) * 4;
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (n0 + n < g.N && k0 + k4 < kend)
-                    v = __ldg(reinterpret_cast<const float4 *>(g.B + (size_t)(n0 + n) * g.ldb + k0 + k4));
-                Bs[(k4 + 0) * LDB_S + n] = v.x;
-                Bs[(k4 + 1) * LDB_S + n] = v.y;
-                Bs[(k4 + 2) * LDB_S + n] = v.z;
-                Bs[(k4 + 3) * LDB_S + n] = v.w;
-            }
-        } else {
-            for (int i = tid; i < kGemmBK * (BN / 4); i += NT) {
-                const int k = i / (BN / 4), n4 = (i % (BN / 4)) * 4;
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (k0 + k < kend && n0 + n4 < g.N)
-                    v = __ldg(reinterpret_cast<const float4 *>(g.B + (size_t)(k0 + k) * g.ldb + n0 + n4));
-                *reinterpret_cast<float4 *>(&Bs[k * LDB_S + n4]) = v;
-            }
-        }
-        __syncthreads();
-#pragma unroll
-        for (int kk = 0; kk < kGemmBK; ++kk) {
-            float a[TM], b[TN];
-#pragma unroll
-            for (int i = 0; i < TM; ++i) a[i] = As[kk * LDA_S + ty * TM + i];
-#pragma unroll
-            for (int j = 0; j < TN; ++j) b[j] = Bs[kk * LDB_S + tx * TN + j];
-#pragma unroll
-            for (int i = 0; i < TM; ++i) {
-                if (want_rs) rs[i] += a[i];
-#pragma unroll
-                for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
-            }
-        }
-        __syncthreads();
+    const bool want_rs = (g.rowsum != nullptr) && bx == 0 && tx == 0;
+    TileLoader<BM, NT, A_KCONTIG> la;
+    TileLoader<BN, NT, B_KCONTIG> lb;
+    if (tid < NT) {
+        la.load(g.A, g.lda, m0, g.M, kbeg, kend, tid);
+        lb.load(g.B, g.ldb, n0, g.N, kbeg, kend, tid);
+        la.store(As, LDA_S, tid);
+        lb.store(Bs, LDB_S, tid);
     }
-    float *C = g.C + (size_t)blockIdx.z * g.M * g.ldc;
+    __syncthreads();
+    for (int k0 = kbeg; k0 < kend; k0 += kGemmBK) {
+        const bool has_next = k0 + kGemmBK < kend;
+        if (has_next && tid < NT) {  // in flight while this tile is multiplied
+            la.load(g.A, g.lda, m0, g.M, k0 + kGemmBK, kend, tid);
+            lb.load(g.B, g.ldb, n0, g.N, k0 + kGemmBK, kend, tid);
+        }
+        if (tid < NT) {
+#pragma unroll
+            for (int kk = 0; kk < kGemmBK; ++kk) {
+                float a[TM], b[TN];
+#pragma unroll
+                for (int i = 0; i < TM; ++i) a[i] = As[kk * LDA_S + ty * TM + i];
+#pragma unroll
+                for (int j = 0; j < TN; ++j) b[j] = Bs[kk * LDB_S + tx * TN + j];
+#pragma unroll
+                for (int i = 0; i < TM; ++i) {
+                    if (want_rs) rs[i] += a[i];
+#pragma unroll
+                    for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+                }
+            }
+        }
+        __syncthreads();
+        if (has_next) {
+            if (tid < NT) {
+                la.store(As, LDA_S, tid);
+                lb.store(Bs, LDB_S, tid);
+            }
+            __syncthreads();
+        }
+    }
+    if (tid >= NT) return;
+    float *C = g.C + (size_t)bz * g.M * g.ldc;
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
         const int m = m0 + ty * TM + i;
@@ -123,18 +148,110 @@ __global__ void __launch_bounds__((BM / TM) * (BN / TN)) gemm_kernel(const GemmA
     }
 }
 
+template <int BM, int BN, int TM, int TN, bool A_KCONTIG, bool B_KCONTIG>
+__global__ void __launch_bounds__((BM / TM) * (BN / TN)) gemm_kernel(const GemmArgs g) {
+    __shared__ __align__(16) float As[kGemmBK * (BM + 4)];
+    __shared__ __align__(16) float Bs[kGemmBK * (BN + 4)];
+    gemm_tile<BM, BN, TM, TN, A_KCONTIG, B_KCONTIG>(g, blockIdx.x, blockIdx.y, blockIdx.z, As, Bs);
+}
+
+// ---------------------------------------------------------------------------------
+// fc2 weight/bias gradient: gW2[j,k] = sum_b dz2[b,j] h[b,k], gb2[j] = sum_b dz2[b,j].
+// Thread = one k (coalesced over h rows), 10 accumulators; the batch is split over CTAs
+// (vy), each split writes its own partial [5056 + 64] (summed by the fused SGD /
+// grad_finalize).  Rows are fetched 16 at a time with all loads issued up front.
+// ---------------------------------------------------------------------------------
+constexpr int kFc2wThreads = 128;
+constexpr int kFc2PartStride = 5120;  // 5000 weights @0, 10 biases @5056
+
+__device__ __forceinline__ void fc2_wgrad_tile(const float *__restrict__ dz2, const float *__restrict__ h,
+                                               float *__restrict__ part, int B, int rows_per_split, int vx, int vy,
+                                               float *ds /* 16*10 floats of shared memory */) {
+    const int t = threadIdx.x, k = vx * kFc2wThreads + t;
+    const int bbeg = vy * rows_per_split, bend = min(B, bbeg + rows_per_split);
+    float acc[kClasses], accb = 0.f;
+#pragma unroll
+    for (int j = 0; j < kClasses; ++j) acc[j] = 0.f;
+    const bool mine = t < kFc2wThreads && k < kHElems;
+    for (int c0 = bbeg; c0 < bend; c0 += 16) {
+        const int nb = min(16, bend - c0);
+        float hv[16];
+#pragma unroll
+        for (int r = 0; r < 16; ++r) hv[r] = (mine && r < nb) ? h[(size_t)(c0 + r) * kHElems + k] : 0.f;
+        __syncthreads();
+        for (int i = t; i < nb * kClasses; i += blockDim.x) ds[i] = dz2[(size_t)c0 * kClasses + i];
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r < nb) {
+#pragma unroll
+                for (int j = 0; j < kClasses; ++j) acc[j] = fmaf(ds[r * kClasses + j], hv[r], acc[j]);
+                if (vx == 0 && t < kClasses) accb += ds[r * kClasses + t];
+            }
+        }
+    }
+    float *p = part + (size_t)vy * kFc2PartStride;
+    if (mine) {
+#pragma unroll
+        for (int j = 0; j < kClasses; ++j) p[j * kHElems + k] = acc[j];
+    }
+    if (vx == 0 && t < kClasses) p[5056 + t] = accb;
+}
+
+__global__ void __launch_bounds__(kFc2wThreads)
+fc2_wgrad_kernel(const float *__restrict__ dz2, const float *__restrict__ h, float *__restrict__ part, int B,
+                 int rows_per_split) {
+    __shared__ float ds[16 * kClasses];
+    fc2_wgrad_tile(dz2, h, part, B, rows_per_split, blockIdx.x, blockIdx.y, ds);
+}
+
+// ---------------------------------------------------------------------------------
+// One launch for the whole backward of the two linear layers (three independent pieces
+// that would otherwise be three dependent launches): CTAs [0, n_wg) compute fc1's weight
+// gradient tiles (64x64, + bias gradient as row sums), the next n_dg CTAs fc1's data
+// gradient tiles (64x32, split-K), the last n_f2 CTAs fc2's weight/bias gradient.
+// ---------------------------------------------------------------------------------
+struct FcBwdArgs {
+    GemmArgs wg, dg;
+    int wg_gx, wg_n;          // fc1 wgrad: grid.x, CTA count
+    int dg_gx, dg_gy, dg_n;   // fc1 dgrad: grid.x, grid.y, CTA count
+    const float *dz2, *h;
+    float *fc2_part;
+    int B, fc2_rows, fc2_gx;
+};
+
+__global__ void __launch_bounds__(256) fc_bwd_kernel(const FcBwdArgs a) {
+    __shared__ __align__(16) float As[kGemmBK * (64 + 4)];
+    __shared__ __align__(16) float Bs[kGemmBK * (64 + 4)];
+    int b = blockIdx.x;
+    if (b < a.wg_n) {
+        gemm_tile<64, 64, 4, 4, false, false>(a.wg, b % a.wg_gx, b / a.wg_gx, 0, As, Bs);
+        return;
+    }
+    b -= a.wg_n;
+    if (b < a.dg_n) {
+        const int per_z = a.dg_gx * a.dg_gy;
+        const int z = b / per_z, r = b - z * per_z;
+        gemm_tile<64, 32, 4, 2, true, false>(a.dg, r % a.dg_gx, r / a.dg_gx, z, As, Bs);
+        return;
+    }
+    b -= a.dg_n;
+    fc2_wgrad_tile(a.dz2, a.h, a.fc2_part, a.B, a.fc2_rows, b % a.fc2_gx, b / a.fc2_gx, As);
+}
+
 // ---------------------------------------------------------------------------------
 // Head: (optional) finish fc1 from its split-K partials + bias + ReLU, then fc2,
 // log_softmax, NLL and the first backward steps, one CTA per batch row:
 //   h      = relu(sum_s part[s][b][:] + b1)           (nsplit > 0; also written to h_out)
-//   z      = h W2^T + b2 ; logp = z - logsumexp(z)      (warp-shuffle dot products)
-//   rows[b]= -logp[target_b]  (mode 0/1)  ;  dz2 = (exp(logp) - onehot) * inv_B
-//   dz1    = (dz2 W2) * (h > 0)
-// The last CTA to finish (threadfence + ticket) reduces rows[] in a fixed order, so the
-// scalar loss is deterministic and needs no second launch.
+//   z      = h W2^T + b2 ; logp = z - logsumexp(z)
+//   rows[b]= -logp[target_b] ;  dz2 = (exp(logp) - onehot) * inv_B ;  dz1 = (dz2 W2) * (h > 0)
+// W2 (20 KB) is staged in shared memory with all loads in flight at once; the 10 dot products
+// are thread-partial sums + warp shuffles.  The last CTA to finish (threadfence + ticket)
+// reduces rows[] in a fixed order, so the scalar loss is deterministic without a second launch.
 //   stats_out[0] = sum(rows) * loss_scale ; stats_out[1] = #(argmax == target) if want_correct
 // ---------------------------------------------------------------------------------
-constexpr int kHeadThreads = 128;
+constexpr int kHeadThreads = 256;
+constexpr int kMaxFc1Split = 10;
 
 struct HeadArgs {
     const float *h_in;      // [B,500] when nsplit == 0
@@ -154,31 +271,68 @@ struct HeadArgs {
 };
 
 __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
+    __shared__ __align__(16) float w2s[kClasses * kHElems];  // 20,000 B
     __shared__ float hs[512];
+    __shared__ float wred[kHeadThreads / 32][kClasses];
     __shared__ float zs[16];
     __shared__ float dzs[16];
     __shared__ float red[kHeadThreads];
     __shared__ float red2[kHeadThreads];
     __shared__ bool is_last;
     const int b = blockIdx.x, t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    for (int k = t; k < kHElems; k += kHeadThreads) {
-        float v;
-        if (a.nsplit > 0) {
-            v = __ldg(a.b1 + k);
-            for (int s = 0; s < a.nsplit; ++s) v += a.part[((size_t)s * a.B + b) * 512 + k];
-            v = fmaxf(v, 0.f);
-            a.h_out[(size_t)b * kHElems + k] = v;
-        } else {
-            v = a.h_in[(size_t)b * kHElems + k];
+    // ---- all global loads of the row up front: W2 tile and this thread's two h elements ----
+    float4 wv[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int i = t + j * kHeadThreads;
+        wv[j] = i < kClasses * kHElems / 4 ? __ldg(reinterpret_cast<const float4 *>(a.w2) + i)
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float hv[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const int k = t + j * kHeadThreads;
+        float v = 0.f;
+        if (k < kHElems) {
+            if (a.nsplit > 0) {
+                v = sum_partials<kMaxFc1Split>(a.part + (size_t)b * 512 + k, a.nsplit, (size_t)a.B * 512);
+                v = fmaxf(v + __ldg(a.b1 + k), 0.f);
+                a.h_out[(size_t)b * kHElems + k] = v;
+            } else {
+                v = a.h_in[(size_t)b * kHElems + k];
+            }
+            hs[k] = v;
         }
-        hs[k] = v;
+        hv[j] = v;
+    }
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int i = t + j * kHeadThreads;
+        if (i < kClasses * kHElems / 4) reinterpret_cast<float4 *>(w2s)[i] = wv[j];
     }
     __syncthreads();
-    for (int j = warp; j < kClasses; j += kHeadThreads / 32) {
+    // ---- z = h W2^T + b2 ----
+    float acc[kClasses];
+#pragma unroll
+    for (int c = 0; c < kClasses; ++c) {
         float s = 0.f;
-        for (int k = lane; k < kHElems; k += 32) s = fmaf(hs[k], __ldg(a.w2 + j * kHElems + k), s);
-        s = warp_sum(s);
-        if (lane == 0) zs[j] = s + __ldg(a.b2 + j);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int k = t + j * kHeadThreads;
+            if (k < kHElems) s = fmaf(hv[j], w2s[c * kHElems + k], s);
+        }
+        acc[c] = warp_sum(s);
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < kClasses; ++c) wred[warp][c] = acc[c];
+    }
+    __syncthreads();
+    if (t < kClasses) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < kHeadThreads / 32; ++w) s += wred[w][t];
+        zs[t] = s + __ldg(a.b2 + t);
     }
     __syncthreads();
     if (t == 0) {
@@ -205,24 +359,25 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
         }
         a.rows[b] = nll;
         if (a.want_correct) a.rows[a.B + b] = (ok && am == (int)tg) ? 1.f : 0.f;
-    }
-    __syncthreads();
-    if (a.dz1) {
-        for (int k = t; k < kHElems; k += kHeadThreads) {
-            float s = 0.f;
-#pragma unroll
-            for (int j = 0; j < kClasses; ++j) s = fmaf(dzs[j], __ldg(a.w2 + j * kHElems + k), s);
-            a.dz1[(size_t)b * kHElems + k] = hs[k] > 0.f ? s : 0.f;
-        }
-    }
-    // ---- deterministic last-CTA reduction of the per-row losses ----
-    if (t == 0) {
         __threadfence();
         const unsigned tk = atomicAdd(a.ticket, 1u);
         is_last = (tk == gridDim.x - 1);
     }
     __syncthreads();
+    if (a.dz1) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int k = t + j * kHeadThreads;
+            if (k < kHElems) {
+                float s = 0.f;
+#pragma unroll
+                for (int c = 0; c < kClasses; ++c) s = fmaf(dzs[c], w2s[c * kHElems + k], s);
+                a.dz1[(size_t)b * kHElems + k] = hv[j] > 0.f ? s : 0.f;
+            }
+        }
+    }
     if (!is_last) return;
+    // ---- deterministic last-CTA reduction of the per-row losses ----
     __threadfence();
     float s = 0.f, c = 0.f;
     for (int r = t; r < a.B; r += kHeadThreads) {
@@ -248,7 +403,7 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
 // autograd bridge; the fused step computes the NLL case inside head_kernel):
 //   dz2 = dlogp - exp(logp) * sum_j dlogp ;  dz1 = (dz2 W2) * (h > 0).   One CTA per row.
 // ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kHeadThreads)
+__global__ void __launch_bounds__(128)
 head_bwd_kernel(const float *__restrict__ logp, const float *__restrict__ dlogp, const float *__restrict__ h,
                 const float *__restrict__ w2, float *__restrict__ dz2, float *__restrict__ dz1) {
     __shared__ float dzs[16];
@@ -265,49 +420,12 @@ head_bwd_kernel(const float *__restrict__ logp, const float *__restrict__ dlogp,
         }
     }
     __syncthreads();
-    for (int k = t; k < kHElems; k += kHeadThreads) {
+    for (int k = t; k < kHElems; k += 128) {
         float s = 0.f;
 #pragma unroll
         for (int j = 0; j < kClasses; ++j) s = fmaf(dzs[j], __ldg(w2 + j * kHElems + k), s);
         dz1[(size_t)b * kHElems + k] = h[(size_t)b * kHElems + k] > 0.f ? s : 0.f;
     }
-}
-
-// ---------------------------------------------------------------------------------
-// fc2 weight/bias gradient: gW2[j,k] = sum_b dz2[b,j] h[b,k], gb2[j] = sum_b dz2[b,j].
-// Thread = one k (coalesced over h rows), 10 accumulators; blockIdx.y splits the batch,
-// each split writes its own partial [5056 + 64] (reduced by grad_finalize / fused SGD).
-// ---------------------------------------------------------------------------------
-constexpr int kFc2wThreads = 128;
-constexpr int kFc2PartStride = 5120;  // 5000 weights @0, 10 biases @5056
-
-__global__ void __launch_bounds__(kFc2wThreads)
-fc2_wgrad_kernel(const float *__restrict__ dz2, const float *__restrict__ h, float *__restrict__ part, int B,
-                 int rows_per_split) {
-    __shared__ float ds[64 * kClasses];
-    const int t = threadIdx.x, k = blockIdx.x * kFc2wThreads + t;
-    const int bbeg = blockIdx.y * rows_per_split, bend = min(B, bbeg + rows_per_split);
-    float acc[kClasses], accb = 0.f;
-#pragma unroll
-    for (int j = 0; j < kClasses; ++j) acc[j] = 0.f;
-    for (int c0 = bbeg; c0 < bend; c0 += 64) {
-        const int nb = min(64, bend - c0);
-        __syncthreads();
-        for (int i = t; i < nb * kClasses; i += kFc2wThreads) ds[i] = dz2[(size_t)c0 * kClasses + i];
-        __syncthreads();
-        for (int r = 0; r < nb; ++r) {
-            const float hv = k < kHElems ? h[(size_t)(c0 + r) * kHElems + k] : 0.f;
-#pragma unroll
-            for (int j = 0; j < kClasses; ++j) acc[j] = fmaf(ds[r * kClasses + j], hv, acc[j]);
-            if (blockIdx.x == 0 && t < kClasses) accb += ds[r * kClasses + t];
-        }
-    }
-    float *p = part + (size_t)blockIdx.y * kFc2PartStride;
-    if (k < kHElems) {
-#pragma unroll
-        for (int j = 0; j < kClasses; ++j) p[j * kHElems + k] = acc[j];
-    }
-    if (blockIdx.x == 0 && t < kClasses) p[5056 + t] = accb;
 }
 
 }  // namespace b200mnist

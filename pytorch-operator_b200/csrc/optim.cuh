@@ -13,9 +13,7 @@ __device__ __forceinline__ float reduce_partials(const GradSegments &segs, int i
             const GradSegment &sg = segs.seg[s];
             const int r = i - sg.off;
             if (r >= 0 && r < sg.n) {
-                float v = __ldcg(sg.part + r);
-                for (int k = 1; k < sg.nsplit; ++k) v += __ldcg(sg.part + (size_t)k * sg.stride + r);
-                return v;
+                return sum_partials<kMaxGradSplit>(sg.part + r, sg.nsplit, (size_t)sg.stride);
             }
         }
     }
@@ -42,9 +40,7 @@ __global__ void __launch_bounds__(256)
 reduce_partials_to_kernel(float *__restrict__ out, const float *__restrict__ part, int n, int nsplit, int stride) {
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
-    float v = __ldcg(part + i);
-    for (int k = 1; k < nsplit; ++k) v += __ldcg(part + (size_t)k * stride + i);
-    out[i] = v;
+    out[i] = sum_partials<kMaxGradSplit>(part + i, nsplit, (size_t)stride);
 }
 
 // One SGD+momentum step over a flat fp32 range, 4 elements per thread.  Rounding matches
