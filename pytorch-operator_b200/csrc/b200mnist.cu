@@ -69,16 +69,16 @@ struct Plan {
 Plan make_plan(int B) {
     Plan p;
     const int gy = ceil_div(B, 64);
-    p.fc1_split = clampi(ceil_div(200, 16 * gy), 1, 10);
+    p.fc1_split = clampi(148 / (16 * gy), 1, 10);  // 16 n-tiles x gy m-tiles x split <= one wave of 148 SMs
     p.fc1_kchunk = ceil_div(ceil_div(800, p.fc1_split), kGemmBK) * kGemmBK;
     p.fc1_split = ceil_div(800, p.fc1_kchunk);
-    p.dg_split = clampi(ceil_div(200, 25 * gy), 1, 8);
+    p.dg_split = clampi(ceil_div(50, 25 * gy), 1, 8);
     p.dg_kchunk = ceil_div(ceil_div(500, p.dg_split), kGemmBK) * kGemmBK;
     p.dg_split = ceil_div(500, p.dg_kchunk);
     p.fc2w_split = clampi(ceil_div(B, 16), 1, 32);
     p.fc2w_rows = ceil_div(B, p.fc2w_split);
     p.fc2w_split = ceil_div(B, p.fc2w_rows);
-    p.c2w_split = clampi(ceil_div(B, 2), 1, 29);
+    p.c2w_split = clampi(ceil_div(B, 2), 1, 32);
     p.c1w_split = clampi(B, 1, kMaxGradSplit);
     p.c2dg_gx = clampi(B, 1, 60);
     return p;
@@ -118,7 +118,7 @@ Workspace carve(void *base, int B) {
     w.fc1_part = static_cast<float *>(take(10 * Bz * 512 * 4));
     w.dp2_part = static_cast<float *>(take(8 * Bz * kP2Elems * 4));
     w.fc2w_part = static_cast<float *>(take((size_t)32 * kFc2PartStride * 4));
-    w.c2w_part = static_cast<float *>(take((size_t)29 * kC2PartStride * 4));
+    w.c2w_part = static_cast<float *>(take((size_t)32 * kC2PartStride * 4));
     w.c1w_part = static_cast<float *>(take((size_t)kMaxGradSplit * kC1PartStride * 4));
     w.bytes = off;
     return w;
@@ -157,7 +157,7 @@ int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h,
     } else {
         g.C = part; g.ldc = 512;
     }
-    gemm_kernel<64, 32, 4, 2, true, true><<<dim3(ceil_div(500, 32), ceil_div(B, 64), pl.fc1_split), 256, 0, s>>>(g);
+    gemm_kernel<64, 32, 2, 4, true, true><<<dim3(ceil_div(500, 32), ceil_div(B, 64), pl.fc1_split), 256, 0, s>>>(g);
     CHECK_LAUNCH("fc1 forward gemm", s);
     *nsplit_out = pl.fc1_split == 1 ? 0 : pl.fc1_split;
     return 0;
@@ -228,9 +228,9 @@ GradSegments step_segments(const Workspace &w, const Plan &pl) {
     s.count = 6;
     return s;
 }
-int launch_finalize(float *grads, const GradSegments &segs, cudaStream_t s) {
+int launch_finalize(float *grads, const GradSegments &segs, const LossReduce &lr, cudaStream_t s) {
     const int n = kFlatElems - (kOffF2W - kOffF1W);
-    grad_finalize_kernel<<<ceil_div(n, 256), 256, 0, s>>>(grads, segs);
+    grad_finalize_kernel<<<ceil_div(n, 256) + 1, 256, 0, s>>>(grads, segs, lr);
     CHECK_LAUNCH("grad finalize", s);
     return 0;
 }
@@ -240,15 +240,16 @@ int reduce_to(float *out, int n, const float *part, int nsplit, int stride, cuda
     CHECK_LAUNCH("partial reduce", s);
     return 0;
 }
-int launch_sgd(float *p, float *g, float *m, int64_t n, float lr, float mu, float scale, int first,
-               const GradSegments *segs, cudaStream_t s) {
+int launch_sgd(float *p, float *g, float *m, int64_t n, float lr, float mu, float scale, int first, cudaStream_t s) {
     const int blocks = (int)((n + 1023) / 1024);
-    if (segs) {
-        sgd_momentum_kernel<true><<<blocks, 256, 0, s>>>(p, g, m, (int)n, -lr, mu, scale, first, *segs);
-    } else {
-        GradSegments none{};
-        sgd_momentum_kernel<false><<<blocks, 256, 0, s>>>(p, g, m, (int)n, -lr, mu, scale, first, none);
-    }
+    GradSegments none{};
+    sgd_momentum_kernel<false><<<blocks, 256, 0, s>>>(p, g, m, (int)n, -lr, mu, scale, first, none);
+    CHECK_LAUNCH("sgd momentum", s);
+    return 0;
+}
+int launch_sgd_fused(float *p, float *g, float *m, float lr, float mu, float scale, int first,
+                     const GradSegments &segs, const LossReduce &lrd, cudaStream_t s) {
+    sgd_fused_kernel<<<kFusedCovBlocks + kFusedFc1Blocks + 1, 256, 0, s>>>(p, g, m, -lr, mu, scale, first, segs, lrd);
     CHECK_LAUNCH("sgd momentum", s);
     return 0;
 }
@@ -268,6 +269,7 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     a.logp = logp_out ? logp_out : w.logp;
     a.dz2 = backward ? w.dz2 : nullptr; a.dz1 = backward ? w.dz1 : nullptr;
     a.rows = w.rows; a.ticket = w.ticket; a.stats_out = stats_out;
+    a.defer_reduce = backward ? 1 : 0;  // training: the step's last kernel reduces the per-row losses
     a.B = B; a.nsplit = nsplit; a.want_correct = want_correct; a.inv_B = 1.0f / (float)B; a.loss_scale = loss_scale;
     if ((rc = launch_head(a, s))) return rc;
     if (!backward) return 0;
@@ -306,7 +308,8 @@ int b200mnist_forward_backward(const float *params, float *grads, const float *x
     const Workspace w = carve(workspace, B);
     if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, logp_out, loss_out, 1.0f / (float)B, 0, s)))
         return rc;
-    return launch_finalize(grads, step_segments(w, pl), s);
+    LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
+    return launch_finalize(grads, step_segments(w, pl), lrd, s);
 }
 
 int b200mnist_train_step(float *params, float *grads, float *momentum, const float *x, const int64_t *target, int B,
@@ -322,7 +325,8 @@ int b200mnist_train_step(float *params, float *grads, float *momentum, const flo
     if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s)))
         return rc;
     const GradSegments segs = step_segments(w, pl);
-    return launch_sgd(params, grads, momentum, kFlatElems, lr, mu, 1.0f, first_step, &segs, s);
+    LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
+    return launch_sgd_fused(params, grads, momentum, lr, mu, 1.0f, first_step, segs, lrd, s);
 }
 
 int b200mnist_forward_eval(const float *params, const float *x, const int64_t *target, int B, void *workspace,
@@ -343,7 +347,7 @@ int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, i
     if (n == 0) return 0;
     if (!aligned16(params) || !aligned16(grads) || !aligned16(momentum))
         return fail_arg(3, "params/grads/momentum must be 16-byte aligned");
-    return launch_sgd(params, const_cast<float *>(grads), momentum, n, lr, mu, grad_scale, first_step, nullptr,
+    return launch_sgd(params, const_cast<float *>(grads), momentum, n, lr, mu, grad_scale, first_step,
                       static_cast<cudaStream_t>(stream));
 }
 
@@ -476,7 +480,7 @@ int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const f
     return reduce_to(gb2, 10, fc2w_part + 5056, pl.fc2w_split, kFc2PartStride, s);
 }
 
-int64_t b200mnist_conv2_bwd_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)29 * kC2PartStride * 4; }
+int64_t b200mnist_conv2_bwd_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)32 * kC2PartStride * 4; }
 
 int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, const float *p1, const float *w, int B,
                         float *gw, float *gb, float *dp1, void *scratch, void *stream) {

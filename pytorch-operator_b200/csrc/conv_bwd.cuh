@@ -12,7 +12,9 @@ constexpr int kMaxDgSplit = 8;  // fc1 data-gradient split-K upper bound (dp2 pa
 // its 2x2 window, ReLU backward kills it where the (post-ReLU) maximum was 0.
 //   D_s : [50][ld] floats, already zero-filled; dp2 may be the sum of `nsplit` partials.
 // All global loads of a thread (<= 4 elements x (nsplit + 2)) are issued before any is used.
-template <int NTHREADS>
+//   PAIRED: rows hold the channel pair {r, r+25} interleaved -- D_s[r*ld + 2*pos + (oc >= 25)] -- so a
+//   128-bit load yields two ready-made (d[oc], d[oc+25]) operand pairs for FFMA2.
+template <int NTHREADS, bool PAIRED = false>
 __device__ __forceinline__ void scatter_dconv2(float *D_s, int ld, const float *__restrict__ dp2, int nsplit,
                                                size_t split_stride, const float *__restrict__ p2,
                                                const uint8_t *__restrict__ i2, size_t b, int tid) {
@@ -36,7 +38,8 @@ __device__ __forceinline__ void scatter_dconv2(float *D_s, int ld, const float *
         if (e < kP2Elems && pv[j] > 0.f) {
             const int oc = e >> 4, p = e & 15;
             const int oy = 2 * (p >> 2) + (q[j] >> 1), ox = 2 * (p & 3) + (q[j] & 1);
-            D_s[oc * ld + oy * 8 + ox] = g[j];
+            if (PAIRED) D_s[(oc >= 25 ? oc - 25 : oc) * ld + 2 * (oy * 8 + ox) + (oc >= 25 ? 1 : 0)] = g[j];
+            else D_s[oc * ld + oy * 8 + ox] = g[j];
         }
     }
 }
@@ -90,29 +93,32 @@ __device__ __forceinline__ void conv2_dgrad_tile(float *smem, const float *__res
         scatter_dconv2<kConvBwdThreads>(D_s, 64, dp2, nsplit, split_stride, p2, i2, (size_t)b, tid);
         __syncthreads();
         if (tm < 25) {
-            float acc[4][8];
+            float2 acc[4][4];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+                for (int j = 0; j < 4; ++j) acc[i][j] = make_float2(0.f, 0.f);
 #pragma unroll 5
             for (int oc = 0; oc < 50; ++oc) {
                 const float4 a = *reinterpret_cast<const float4 *>(&W_s[oc * 100 + tm * 4]);
                 const float4 b0 = *reinterpret_cast<const float4 *>(&D_s[oc * 64 + tn * 4]);
                 const float4 b1 = *reinterpret_cast<const float4 *>(&D_s[oc * 64 + 32 + tn * 4]);
                 const float av[4] = {a.x, a.y, a.z, a.w};
-                const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                const float2 bv[4] = {make_float2(b0.x, b0.y), make_float2(b0.z, b0.w), make_float2(b1.x, b1.y),
+                                      make_float2(b1.z, b1.w)};
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < 4; ++i) {
+                    const float2 aa = make_float2(av[i], av[i]);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+                    for (int j = 0; j < 4; ++j) acc[i][j] = __ffma2_rn(aa, bv[j], acc[i][j]);
+                }
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 float *row = &T_s[(tm * 4 + i) * kDgLdT];
-                *reinterpret_cast<float4 *>(row + tn * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+                *reinterpret_cast<float4 *>(row + tn * 4) = make_float4(acc[i][0].x, acc[i][0].y, acc[i][1].x, acc[i][1].y);
                 *reinterpret_cast<float4 *>(row + 32 + tn * 4) =
-                    make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+                    make_float4(acc[i][2].x, acc[i][2].y, acc[i][3].x, acc[i][3].y);
             }
         }
         __syncthreads();
@@ -146,24 +152,24 @@ __device__ __forceinline__ void conv2_dgrad_tile(float *smem, const float *__res
 // batch slices are summed in a fixed order by grad_finalize / the fused SGD kernel.
 // ---------------------------------------------------------------------------------
 constexpr int kWgIcPerCta = 4;
-constexpr int kWgLdD = 68;
+constexpr int kWgLdD = 132;  // floats per channel-pair row: 2 x 64 interleaved + 4 pad (conflict-free LDS.128)
 constexpr int kC2PartStride = 25088;  // 25,000 weights @0, 50 biases @25,024
-constexpr int kWgSmemFloats = 2 * kWgIcPerCta * 144 + 2 * 50 * kWgLdD;  // 7,952 floats
+constexpr int kWgSmemFloats = 2 * kWgIcPerCta * 144 + 2 * 25 * kWgLdD;  // 7,752 floats
 
 __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__restrict__ dp2, int nsplit,
                                                  size_t split_stride, const float *__restrict__ p2,
                                                  const uint8_t *__restrict__ i2, const float *__restrict__ p1,
                                                  float *__restrict__ part, int B, int vx, int vy, int gy) {
     float *P_s = smem;                                // [2][4 ic][144]
-    float *D_s = smem + 2 * kWgIcPerCta * 144;        // [2][50][68]   (later: the 50 x 100 output tile)
+    float *D_s = smem + 2 * kWgIcPerCta * 144;        // [2][25 pairs][132] (later: the 50 x 100 output tile)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, icl = warp & 3, par = warp >> 2;
     const int ic0 = vx * kWgIcPerCta;
     const bool active = lane < 25;
-    float acc0[5][5], acc1[5][5], accb0 = 0.f, accb1 = 0.f;
+    float2 acc[5][5], accb = make_float2(0.f, 0.f);  // .x: channel `lane`, .y: channel `lane + 25`
 #pragma unroll
     for (int i = 0; i < 5; ++i)
 #pragma unroll
-        for (int j = 0; j < 5; ++j) acc0[i][j] = acc1[i][j] = 0.f;
+        for (int j = 0; j < 5; ++j) acc[i][j] = make_float2(0.f, 0.f);
 
     for (int bb = vy * 2; bb < B; bb += gy * 2) {
         __syncthreads();  // previous trip's readers are done
@@ -178,7 +184,7 @@ __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__res
                     if (b < B) pv[j] = __ldg(reinterpret_cast<const float4 *>(p1 + (size_t)b * kP1Elems + ic0 * 144) + r);
                 }
             }
-            for (int i = tid; i < 2 * 50 * kWgLdD / 4; i += kConvBwdThreads)
+            for (int i = tid; i < 2 * 25 * kWgLdD / 4; i += kConvBwdThreads)
                 reinterpret_cast<float4 *>(D_s)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
@@ -187,15 +193,14 @@ __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__res
             }
         }
         __syncthreads();
-        scatter_dconv2<kConvBwdThreads>(D_s, kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb, tid);
+        scatter_dconv2<kConvBwdThreads, true>(D_s, kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb, tid);
         if (bb + 1 < B)
-            scatter_dconv2<kConvBwdThreads>(D_s + 50 * kWgLdD, kWgLdD, dp2, nsplit, split_stride, p2, i2,
-                                            (size_t)bb + 1, tid);
+            scatter_dconv2<kConvBwdThreads, true>(D_s + 25 * kWgLdD, kWgLdD, dp2, nsplit, split_stride, p2, i2,
+                                                  (size_t)bb + 1, tid);
         __syncthreads();
         if (active && bb + par < B) {
             const float *ps = P_s + (par * kWgIcPerCta + icl) * 144;
-            const float *d0p = D_s + par * 50 * kWgLdD + lane * kWgLdD;
-            const float *d1p = d0p + 25 * kWgLdD;
+            const float *dp = D_s + (par * 25 + lane) * kWgLdD;
 #pragma unroll 1
             for (int oy = 0; oy < 8; ++oy) {
                 float strip[5][12];
@@ -207,21 +212,22 @@ __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__res
                         strip[r][4 * j] = v.x; strip[r][4 * j + 1] = v.y;
                         strip[r][4 * j + 2] = v.z; strip[r][4 * j + 3] = v.w;
                     }
-                const float4 da = *reinterpret_cast<const float4 *>(d0p + oy * 8);
-                const float4 db = *reinterpret_cast<const float4 *>(d0p + oy * 8 + 4);
-                const float4 dc = *reinterpret_cast<const float4 *>(d1p + oy * 8);
-                const float4 dd = *reinterpret_cast<const float4 *>(d1p + oy * 8 + 4);
-                const float d0[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
-                const float d1[8] = {dc.x, dc.y, dc.z, dc.w, dd.x, dd.y, dd.z, dd.w};
+                float2 d[8];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 v = *reinterpret_cast<const float4 *>(dp + oy * 16 + 4 * j);
+                    d[2 * j] = make_float2(v.x, v.y);
+                    d[2 * j + 1] = make_float2(v.z, v.w);
+                }
 #pragma unroll
                 for (int ox = 0; ox < 8; ++ox) {
-                    if (icl == 0) { accb0 += d0[ox]; accb1 += d1[ox]; }
+                    if (icl == 0) { accb.x += d[ox].x; accb.y += d[ox].y; }
 #pragma unroll
                     for (int ky = 0; ky < 5; ++ky)
 #pragma unroll
                         for (int kx = 0; kx < 5; ++kx) {
-                            acc0[ky][kx] = fmaf(d0[ox], strip[ky][ox + kx], acc0[ky][kx]);
-                            acc1[ky][kx] = fmaf(d1[ox], strip[ky][ox + kx], acc1[ky][kx]);
+                            const float sv = strip[ky][ox + kx];
+                            acc[ky][kx] = __ffma2_rn(d[ox], make_float2(sv, sv), acc[ky][kx]);
                         }
                 }
             }
@@ -235,10 +241,10 @@ __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__res
         for (int ky = 0; ky < 5; ++ky)
 #pragma unroll
             for (int kx = 0; kx < 5; ++kx) {
-                O_s[lane * 100 + icl * 25 + ky * 5 + kx] = acc0[ky][kx];
-                O_s[(lane + 25) * 100 + icl * 25 + ky * 5 + kx] = acc1[ky][kx];
+                O_s[lane * 100 + icl * 25 + ky * 5 + kx] = acc[ky][kx].x;
+                O_s[(lane + 25) * 100 + icl * 25 + ky * 5 + kx] = acc[ky][kx].y;
             }
-        if (icl == 0) { O_s[5000 + lane] = accb0; O_s[5000 + lane + 25] = accb1; }
+        if (icl == 0) { O_s[5000 + lane] = accb.x; O_s[5000 + lane + 25] = accb.y; }
     }
     __syncthreads();
     if (par == 0 && active) {
@@ -246,10 +252,10 @@ __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__res
         for (int ky = 0; ky < 5; ++ky)
 #pragma unroll
             for (int kx = 0; kx < 5; ++kx) {
-                O_s[lane * 100 + icl * 25 + ky * 5 + kx] += acc0[ky][kx];
-                O_s[(lane + 25) * 100 + icl * 25 + ky * 5 + kx] += acc1[ky][kx];
+                O_s[lane * 100 + icl * 25 + ky * 5 + kx] += acc[ky][kx].x;
+                O_s[(lane + 25) * 100 + icl * 25 + ky * 5 + kx] += acc[ky][kx].y;
             }
-        if (icl == 0) { O_s[5000 + lane] += accb0; O_s[5000 + lane + 25] += accb1; }
+        if (icl == 0) { O_s[5000 + lane] += accb.x; O_s[5000 + lane + 25] += accb.y; }
     }
     __syncthreads();
     float *po = part + (size_t)vy * kC2PartStride;
@@ -288,11 +294,12 @@ __global__ void __launch_bounds__(kConvBwdThreads) conv2_bwd_kernel(const Conv2B
 // ---------------------------------------------------------------------------------
 // conv1 weight/bias gradient (the input image needs no gradient).  The conv1 output
 // gradient has one non-zero per 2x2 window (pool arg-max) and none where ReLU was inactive,
-// so the sum is taken sparsely: warp = channel, lane = filter tap (25 active, lane 25 sums
-// the bias gradient).  A lane first fetches the gradient / arg-max of its share of the 144
-// windows (5 independent loads each of p1, dp1, idx), then the values are broadcast with
-// shuffles and windows with a zero gradient are skipped.  grid = (batch slices, 2 channel
-// halves); each CTA writes a partial [512 + 64] (its half of the channels).
+// so the sum is taken sparsely.  warp = channel, lane = filter tap (25 active, lane 25 sums
+// the bias gradient).  Per (image, channel) the warp first builds, in shared memory, the
+// compacted list of its non-zero windows as (gradient, input offset) pairs -- 5 independent
+// loads per lane, ballot + popc prefix -- then every lane walks the list: one broadcast
+// LDS.64 for the pair, one LDS for its input pixel, one FMA, four entries in flight.
+// grid = (batch slices, 2 channel halves); each CTA writes a partial [512 + 64].
 // ---------------------------------------------------------------------------------
 constexpr int kC1wThreads = 320;    // 10 channels x 32 lanes
 constexpr int kC1PartStride = 576;  // 500 weights @0, 20 biases @512
@@ -301,9 +308,11 @@ __global__ void __launch_bounds__(kC1wThreads)
 conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
                    const uint8_t *__restrict__ i1, float *__restrict__ part, int B) {
     __shared__ __align__(16) float xs[kXElems];
-    const int tid = threadIdx.x, c = blockIdx.y * 10 + (tid >> 5), lane = tid & 31;
-    const int ky = lane / 5, kx = lane - ky * 5;  // lanes >= 25: unused taps
-    float acc = 0.f;
+    __shared__ __align__(8) float2 lst[10][160];
+    const int tid = threadIdx.x, wid = tid >> 5, c = blockIdx.y * 10 + wid, lane = tid & 31;
+    const int ky = lane / 5, kx = lane - ky * 5;
+    const int tap = lane < 25 ? ky * 28 + kx : 0;
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
     for (int b = blockIdx.x; b < B; b += gridDim.x) {
         const size_t base = ((size_t)b * 20 + c) * 144;
         float gl[5];
@@ -323,23 +332,34 @@ conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, c
                 ol[j] = (2 * (wl / 12) + (q >> 1)) * 28 + 2 * (wl % 12) + (q & 1);
             }
         }
-        __syncthreads();  // previous image's readers of xs are done
+        __syncthreads();  // previous image's readers of xs / lst are done
         if (tid < kXElems / 4) reinterpret_cast<float4 *>(xs)[tid] = xv;
-        __syncthreads();
+        int n = 0;
 #pragma unroll
         for (int j = 0; j < 5; ++j) {
-            const int cnt = j < 4 ? 32 : 16;
-#pragma unroll 4
-            for (int l = 0; l < cnt; ++l) {
-                const float g = __shfl_sync(0xffffffffu, gl[j], l);
-                const int o = __shfl_sync(0xffffffffu, ol[j], l);
-                if (g != 0.f) {
-                    if (lane < 25) acc = fmaf(g, xs[o + ky * 28 + kx], acc);
-                    else if (lane == 25) acc += g;
-                }
+            const bool nz = gl[j] != 0.f;
+            const unsigned m = __ballot_sync(0xffffffffu, nz);
+            if (nz) lst[wid][n + __popc(m & ((1u << lane) - 1u))] = make_float2(gl[j], __int_as_float(ol[j]));
+            n += __popc(m);
+        }
+        if (lane < 4) lst[wid][n + lane] = make_float2(0.f, __int_as_float(0));  // pad to a multiple of 4
+        __syncthreads();
+        const float2 *l = lst[wid];
+        if (lane < 25) {
+            for (int i = 0; i < n; i += 4) {
+                const float2 e0 = l[i], e1 = l[i + 1], e2 = l[i + 2], e3 = l[i + 3];
+                acc0 = fmaf(e0.x, xs[__float_as_int(e0.y) + tap], acc0);
+                acc1 = fmaf(e1.x, xs[__float_as_int(e1.y) + tap], acc1);
+                acc2 = fmaf(e2.x, xs[__float_as_int(e2.y) + tap], acc2);
+                acc3 = fmaf(e3.x, xs[__float_as_int(e3.y) + tap], acc3);
+            }
+        } else if (lane == 25) {
+            for (int i = 0; i < n; i += 4) {
+                acc0 += l[i].x; acc1 += l[i + 1].x; acc2 += l[i + 2].x; acc3 += l[i + 3].x;
             }
         }
     }
+    const float acc = (acc0 + acc1) + (acc2 + acc3);
     float *po = part + (size_t)blockIdx.x * kC1PartStride;
     if (lane < 25) po[c * 25 + lane] = acc;
     else if (lane == 25) po[512 + c] = acc;

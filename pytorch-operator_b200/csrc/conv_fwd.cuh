@@ -1,4 +1,7 @@
 // Forward kernels for the two conv5x5 + ReLU + 2x2 max-pool stages (mnist.py:26-29).
+// All multiply-adds are issued as packed FFMA2 (fma.rn.f32x2, new on sm_100): two fp32 FMAs per
+// lane per instruction, IEEE-identical to scalar FFMA, pairing two OUTPUT CHANNELS so that the
+// weight pair comes straight out of a 64/128-bit shared-memory load.
 #pragma once
 #include "common.cuh"
 
@@ -6,26 +9,29 @@ namespace b200mnist {
 
 // ---------------------------------------------------------------------------------
 // conv1: 1 -> 20 channels on 28x28 (K = 25 per output: not a contraction worth a tensor
-// core).  One CTA = one image x 5 output channels; the 28x28 image is staged once in
+// core).  One CTA = one image x 4 output channels; the 28x28 image is staged once in
 // shared memory, each thread owns one pooled pixel: its 6x6 input patch sits in registers
-// and is reused for the 4 conv outputs of the window and for all 5 channels (weights are
-// warp-uniform shared-memory broadcasts).  ReLU, max and arg-max are taken in registers,
-// so the 24x24 conv map never exists in memory.
+// and is reused for the 4 conv outputs of the window and for all 4 channels (weights are
+// warp-uniform LDS.128 broadcasts of [tap][4 channels]).  ReLU, max and arg-max are taken in
+// registers, so the 24x24 conv map never exists in memory.
 // ---------------------------------------------------------------------------------
-constexpr int kC1ChPerCta = 5;
+constexpr int kC1ChPerCta = 4;
 constexpr int kC1Threads = 160;
 
 __global__ void __launch_bounds__(kC1Threads)
 conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ bias,
                            float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
     __shared__ __align__(16) float xs[kXElems];
-    __shared__ float ws[kC1ChPerCta * 25];
+    __shared__ __align__(16) float ws[25 * kC1ChPerCta];
     __shared__ float bs[kC1ChPerCta];
     const int b = blockIdx.x, c0 = blockIdx.y * kC1ChPerCta, t = threadIdx.x;
     const float4 *xg = reinterpret_cast<const float4 *>(x + (size_t)b * kXElems);
-    for (int i = t; i < kXElems / 4; i += kC1Threads) reinterpret_cast<float4 *>(xs)[i] = __ldg(xg + i);
-    if (t < kC1ChPerCta * 25) ws[t] = __ldg(w + c0 * 25 + t);
+    float4 xv0 = __ldg(xg + t), xv1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t + kC1Threads < kXElems / 4) xv1 = __ldg(xg + t + kC1Threads);
+    if (t < 25 * kC1ChPerCta) ws[(t % 25) * kC1ChPerCta + t / 25] = __ldg(w + c0 * 25 + t);
     if (t < kC1ChPerCta) bs[t] = __ldg(bias + c0 + t);
+    reinterpret_cast<float4 *>(xs)[t] = xv0;
+    if (t + kC1Threads < kXElems / 4) reinterpret_cast<float4 *>(xs)[t + kC1Threads] = xv1;
     __syncthreads();
     if (t >= 144) return;
     const int py = t / 12, px = t % 12;
@@ -38,19 +44,34 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
             patch[r][2 * j] = v.x;
             patch[r][2 * j + 1] = v.y;
         }
+    float2 acc[2][4];  // [channel pair][window slot]
+#pragma unroll
+    for (int cp = 0; cp < 2; ++cp)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[cp][q] = make_float2(bs[2 * cp], bs[2 * cp + 1]);
+#pragma unroll
+    for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 5; ++kx) {
+            const float4 w4 = *reinterpret_cast<const float4 *>(&ws[(ky * 5 + kx) * kC1ChPerCta]);
+            const float2 wp[2] = {make_float2(w4.x, w4.y), make_float2(w4.z, w4.w)};
+            const float2 p00 = make_float2(patch[ky][kx], patch[ky][kx]);
+            const float2 p01 = make_float2(patch[ky][kx + 1], patch[ky][kx + 1]);
+            const float2 p10 = make_float2(patch[ky + 1][kx], patch[ky + 1][kx]);
+            const float2 p11 = make_float2(patch[ky + 1][kx + 1], patch[ky + 1][kx + 1]);
+#pragma unroll
+            for (int cp = 0; cp < 2; ++cp) {
+                acc[cp][0] = __ffma2_rn(wp[cp], p00, acc[cp][0]);
+                acc[cp][1] = __ffma2_rn(wp[cp], p01, acc[cp][1]);
+                acc[cp][2] = __ffma2_rn(wp[cp], p10, acc[cp][2]);
+                acc[cp][3] = __ffma2_rn(wp[cp], p11, acc[cp][3]);
+            }
+        }
 #pragma unroll
     for (int c = 0; c < kC1ChPerCta; ++c) {
-        float a0 = bs[c], a1 = a0, a2 = a0, a3 = a0;
-#pragma unroll
-        for (int ky = 0; ky < 5; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 5; ++kx) {
-                const float wv = ws[c * 25 + ky * 5 + kx];
-                a0 = fmaf(wv, patch[ky][kx], a0);
-                a1 = fmaf(wv, patch[ky][kx + 1], a1);
-                a2 = fmaf(wv, patch[ky + 1][kx], a2);
-                a3 = fmaf(wv, patch[ky + 1][kx + 1], a3);
-            }
+        const int cp = c >> 1;
+        const float a0 = (c & 1) ? acc[cp][0].y : acc[cp][0].x, a1 = (c & 1) ? acc[cp][1].y : acc[cp][1].x;
+        const float a2 = (c & 1) ? acc[cp][2].y : acc[cp][2].x, a3 = (c & 1) ? acc[cp][3].y : acc[cp][3].x;
         float best = a0;
         int bi = 0;
         if (a1 > best) { best = a1; bi = 1; }
@@ -63,17 +84,17 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
 }
 
 // ---------------------------------------------------------------------------------
-// Register-tiled 5x5 direct convolution micro-kernel shared by conv2 forward:
-// one thread accumulates a 2x2 block of outputs for 10 output channels
-// (40 accumulators) over input channels [c_begin, c_end).  Per input channel it loads
-// the 6x6 patch once (18 LDS.64) and, per tap, the 10 channel weights as a warp-uniform
-// broadcast (2 LDS.128 + 1 LDS.64): 1000 FMA per 93 shared-memory loads.
+// Register-tiled 5x5 direct convolution micro-kernel of conv2 forward: one thread
+// accumulates a 2x2 block of outputs for 10 output channels (20 packed accumulators) over
+// input channels [c_begin, c_end).  Per input channel it loads the 6x6 patch once
+// (18 LDS.64) and, per tap, the 5 channel-pair weights as a warp-uniform broadcast
+// (2 LDS.128 + 1 LDS.64) feeding 20 FFMA2: 500 FFMA2 (= 1000 MAC) per 93 shared-memory loads.
 //   in_s : this lane's image, planes of `plane` floats, rows of IW floats
-//   w_s  : [cin][25 taps][12] (10 output channels + 2 pad), 16-byte aligned rows
+//   w_s  : [cin*25 taps][12] (10 output channels + 2 pad), 16-byte aligned rows
 // ---------------------------------------------------------------------------------
 template <int IW>
 __device__ __forceinline__ void conv5_tile_accum(const float *in_s, int plane, const float *w_s, int c_begin,
-                                                 int c_end, int r0, int c0, float (&acc)[10][4]) {
+                                                 int c_end, int r0, int c0, float2 (&acc)[5][4]) {
     for (int c = c_begin; c < c_end; ++c) {
         const float *pl = in_s + c * plane + r0 * IW + c0;
         float patch[6][6];
@@ -94,13 +115,18 @@ __device__ __forceinline__ void conv5_tile_accum(const float *in_s, int plane, c
                 const float4 w0 = *reinterpret_cast<const float4 *>(wp);
                 const float4 w1 = *reinterpret_cast<const float4 *>(wp + 4);
                 const float2 w2 = *reinterpret_cast<const float2 *>(wp + 8);
-                const float wv[10] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y};
+                const float2 wv[5] = {make_float2(w0.x, w0.y), make_float2(w0.z, w0.w), make_float2(w1.x, w1.y),
+                                      make_float2(w1.z, w1.w), w2};
+                const float2 p00 = make_float2(patch[ky][kx], patch[ky][kx]);
+                const float2 p01 = make_float2(patch[ky][kx + 1], patch[ky][kx + 1]);
+                const float2 p10 = make_float2(patch[ky + 1][kx], patch[ky + 1][kx]);
+                const float2 p11 = make_float2(patch[ky + 1][kx + 1], patch[ky + 1][kx + 1]);
 #pragma unroll
-                for (int o = 0; o < 10; ++o) {
-                    acc[o][0] = fmaf(wv[o], patch[ky][kx], acc[o][0]);
-                    acc[o][1] = fmaf(wv[o], patch[ky][kx + 1], acc[o][1]);
-                    acc[o][2] = fmaf(wv[o], patch[ky + 1][kx], acc[o][2]);
-                    acc[o][3] = fmaf(wv[o], patch[ky + 1][kx + 1], acc[o][3]);
+                for (int o = 0; o < 5; ++o) {
+                    acc[o][0] = __ffma2_rn(wv[o], p00, acc[o][0]);
+                    acc[o][1] = __ffma2_rn(wv[o], p01, acc[o][1]);
+                    acc[o][2] = __ffma2_rn(wv[o], p10, acc[o][2]);
+                    acc[o][3] = __ffma2_rn(wv[o], p11, acc[o][3]);
                 }
             }
     }
@@ -108,27 +134,30 @@ __device__ __forceinline__ void conv5_tile_accum(const float *in_s, int plane, c
 
 // ---------------------------------------------------------------------------------
 // conv2: 20 -> 50 channels on 12x12, K = 500 per output (70% of the forward MACs).
-// One CTA = 2 images x 10 output channels.  The 4 warps split the 20 input channels
-// (5 each); a lane is (image, pooled pixel), so all lanes of a warp share the weight
-// address (broadcast) and hit distinct banks for the activation patch.  The 4 partial
-// sums are combined through shared memory (aliasing the image tile), then bias, ReLU,
-// max and arg-max are applied and only the pooled 4x4 map is written.
+// One CTA = 2 images x 10 output channels; the 4 warps split the 20 input channels (5 each, one
+// warp per SM sub-partition);
+// a lane is (image, pooled pixel), so all lanes of a warp share the weight address
+// (broadcast) and hit distinct banks for the activation patch.  The 5 partial sums are
+// combined through shared memory (aliasing the staged operands), then bias, ReLU, max and
+// arg-max are applied and only the pooled 4x4 map is written.
 // ---------------------------------------------------------------------------------
 constexpr int kC2ImgPerCta = 2;
 constexpr int kC2OcPerCta = 10;
-constexpr int kC2Threads = 128;
+constexpr int kC2Warps = 4;
+constexpr int kC2Threads = kC2Warps * 32;
 
 __global__ void __launch_bounds__(kC2Threads)
 conv2_relu_pool_fwd_kernel(const float *__restrict__ in, const float *__restrict__ w, const float *__restrict__ bias,
                            float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
-    __shared__ __align__(16) float in_s[kC2ImgPerCta * kP1Elems];  // 23,040 B; later the 4x40x32 reduce buffer
-    __shared__ __align__(16) float w_s[500 * 12];                  // 24,000 B
+    __shared__ __align__(16) float smem_c2[kC2ImgPerCta * kP1Elems + 500 * 12];  // 23,040 + 24,000 B
+    float *in_s = smem_c2;                            // [2][20][144]
+    float *w_s = smem_c2 + kC2ImgPerCta * kP1Elems;   // [500][12]
     const int t = threadIdx.x, b0 = blockIdx.x * kC2ImgPerCta, oc0 = blockIdx.y * kC2OcPerCta;
     {   // stage both operands with every global load in flight before the first store
-        constexpr int kImgVec = kC2ImgPerCta * kP1Elems / 4;        // 1440 float4
-        constexpr int kWVec = kC2OcPerCta * 500 / 4;                // 1250 float4 (10 contiguous rows of W)
-        constexpr int kImgPer = (kImgVec + kC2Threads - 1) / kC2Threads, kWPer = (kWVec + kC2Threads - 1) / kC2Threads;
-        float4 iv[kImgPer], wv[kWPer];
+        constexpr int kImgVec = kC2ImgPerCta * kP1Elems / 4;                    // 1440 float4
+        constexpr int kImgPer = (kImgVec + kC2Threads - 1) / kC2Threads;        // 9
+        constexpr int kTapPer = (500 + kC2Threads - 1) / kC2Threads;            // 4
+        float4 iv[kImgPer];
 #pragma unroll
         for (int j = 0; j < kImgPer; ++j) {
             const int i = t + j * kC2Threads;
@@ -138,11 +167,14 @@ conv2_relu_pool_fwd_kernel(const float *__restrict__ in, const float *__restrict
                 if (b < B) iv[j] = __ldg(reinterpret_cast<const float4 *>(in + (size_t)b * kP1Elems) + (i - img * (kP1Elems / 4)));
             }
         }
-        const float4 *wg = reinterpret_cast<const float4 *>(w + (size_t)oc0 * 500);
+        // weights: a thread owns taps r = t + j*160 and gathers their 10 output channels (each load
+        // is coalesced across the warp), then writes each tap row with three 16-byte stores.
+        float wv[kTapPer][kC2OcPerCta];
 #pragma unroll
-        for (int j = 0; j < kWPer; ++j) {
-            const int i = t + j * kC2Threads;
-            wv[j] = i < kWVec ? __ldg(wg + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < kTapPer; ++j) {
+            const int r = t + j * kC2Threads;
+#pragma unroll
+            for (int o = 0; o < kC2OcPerCta; ++o) wv[j][o] = r < 500 ? __ldg(w + (size_t)(oc0 + o) * 500 + r) : 0.f;
         }
 #pragma unroll
         for (int j = 0; j < kImgPer; ++j) {
@@ -150,55 +182,64 @@ conv2_relu_pool_fwd_kernel(const float *__restrict__ in, const float *__restrict
             if (i < kImgVec) reinterpret_cast<float4 *>(in_s)[i] = iv[j];
         }
 #pragma unroll
-        for (int j = 0; j < kWPer; ++j) {
-            const int i = t + j * kC2Threads;
-            if (i < kWVec) {  // element e = 4*i of the [10][500] block -> w_s[(ic*25+k)][oc]
-                const float v[4] = {wv[j].x, wv[j].y, wv[j].z, wv[j].w};
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int e = 4 * i + u, oc = e / 500, r = e - oc * 500;
-                    w_s[r * 12 + oc] = v[u];
-                }
+        for (int j = 0; j < kTapPer; ++j) {
+            const int r = t + j * kC2Threads;
+            if (r < 500) {
+                float4 *row = reinterpret_cast<float4 *>(w_s + r * 12);
+                row[0] = make_float4(wv[j][0], wv[j][1], wv[j][2], wv[j][3]);
+                row[1] = make_float4(wv[j][4], wv[j][5], wv[j][6], wv[j][7]);
+                row[2] = make_float4(wv[j][8], wv[j][9], 0.f, 0.f);
             }
         }
     }
     __syncthreads();
-    const int warp = t >> 5, lane = t & 31, img = lane >> 4, pos = lane & 15, py = pos >> 2, px = pos & 3;
-    float acc[10][4];
+    const int warp = t >> 5, lane = t & 31;
+    const int img = lane >> 4, pos = lane & 15, py = pos >> 2, px = pos & 3;
+    float2 acc[5][4];
 #pragma unroll
-    for (int o = 0; o < 10; ++o)
+    for (int o = 0; o < 5; ++o)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[o][q] = 0.f;
+        for (int q = 0; q < 4; ++q) acc[o][q] = make_float2(0.f, 0.f);
     conv5_tile_accum<12>(in_s + img * kP1Elems, 144, w_s, warp * 5, warp * 5 + 5, 2 * py, 2 * px, acc);
-    __syncthreads();  // all patches read; in_s becomes the reduce buffer
-    float *red = in_s;
+    __syncthreads();  // all operands consumed; the buffer becomes the reduce area
+    float2 *red = reinterpret_cast<float2 *>(smem_c2);  // [warp][pair o][slot q][32 lanes] float2 = 25,600 B
 #pragma unroll
-    for (int o = 0; o < 10; ++o)
+    for (int o = 0; o < 5; ++o)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) red[(warp * 40 + o * 4 + q) * 32 + lane] = acc[o][q];
+        for (int q = 0; q < 4; ++q) red[((warp * 5 + o) * 4 + q) * 32 + lane] = acc[o][q];
     __syncthreads();
+    // warp w finishes channel pair w (and warp 0 also pair 4): channels 2*pr and 2*pr+1
     const int b = b0 + img;
-    for (int o = warp; o < 10; o += 4) {
-        const float bv = __ldg(bias + oc0 + o);
-        float v[4];
+    for (int pr = warp; pr < 5; pr += kC2Warps) {
+    float2 v[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            float s = red[(0 * 40 + o * 4 + q) * 32 + lane];
-            s += red[(1 * 40 + o * 4 + q) * 32 + lane];
-            s += red[(2 * 40 + o * 4 + q) * 32 + lane];
-            s += red[(3 * 40 + o * 4 + q) * 32 + lane];
-            v[q] = s + bv;
+    for (int q = 0; q < 4; ++q) {
+        float2 s = red[((0 * 5 + pr) * 4 + q) * 32 + lane];
+#pragma unroll
+        for (int g = 1; g < kC2Warps; ++g) {
+            const float2 r = red[((g * 5 + pr) * 4 + q) * 32 + lane];
+            s.x += r.x;
+            s.y += r.y;
         }
-        float best = v[0];
+        v[q] = s;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int oc = 2 * pr + h;
+        const float bv = __ldg(bias + oc0 + oc);
+        const float c0v = (h ? v[0].y : v[0].x) + bv, c1v = (h ? v[1].y : v[1].x) + bv;
+        const float c2v = (h ? v[2].y : v[2].x) + bv, c3v = (h ? v[3].y : v[3].x) + bv;
+        float best = c0v;
         int bi = 0;
-        if (v[1] > best) { best = v[1]; bi = 1; }
-        if (v[2] > best) { best = v[2]; bi = 2; }
-        if (v[3] > best) { best = v[3]; bi = 3; }
+        if (c1v > best) { best = c1v; bi = 1; }
+        if (c2v > best) { best = c2v; bi = 2; }
+        if (c3v > best) { best = c3v; bi = 3; }
         if (b < B) {
-            const size_t oidx = ((size_t)b * 50 + oc0 + o) * 16 + pos;
+            const size_t oidx = ((size_t)b * 50 + oc0 + oc) * 16 + pos;
             out[oidx] = fmaxf(best, 0.f);
             idx[oidx] = (uint8_t)bi;
         }
+    }
     }
 }
 

@@ -80,13 +80,14 @@ __device__ __forceinline__ void gemm_tile(const GemmArgs &g, int bx, int by, int
     const int tid = threadIdx.x, tx = tid % (BN / TN), ty = tid / (BN / TN);
     const int m0 = by * BM, n0 = bx * BN;
     const int kbeg = bz * g.kchunk, kend = min(g.K, kbeg + g.kchunk);
-    float acc[TM][TN];
+    static_assert(TN % 2 == 0, "accumulators are packed in pairs along n (FFMA2)");
+    float2 acc[TM][TN / 2];
     float rs[TM];
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
         rs[i] = 0.f;
 #pragma unroll
-        for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+        for (int j = 0; j < TN / 2; ++j) acc[i][j] = make_float2(0.f, 0.f);
     }
     const bool want_rs = (g.rowsum != nullptr) && bx == 0 && tx == 0;
     TileLoader<BM, NT, A_KCONTIG> la;
@@ -107,16 +108,18 @@ __device__ __forceinline__ void gemm_tile(const GemmArgs &g, int bx, int by, int
         if (tid < NT) {
 #pragma unroll
             for (int kk = 0; kk < kGemmBK; ++kk) {
-                float a[TM], b[TN];
+                float a[TM];
+                float2 b[TN / 2];
 #pragma unroll
                 for (int i = 0; i < TM; ++i) a[i] = As[kk * LDA_S + ty * TM + i];
 #pragma unroll
-                for (int j = 0; j < TN; ++j) b[j] = Bs[kk * LDB_S + tx * TN + j];
+                for (int j = 0; j < TN / 2; ++j) b[j] = *reinterpret_cast<const float2 *>(&Bs[kk * LDB_S + tx * TN + 2 * j]);
 #pragma unroll
                 for (int i = 0; i < TM; ++i) {
                     if (want_rs) rs[i] += a[i];
+                    const float2 aa = make_float2(a[i], a[i]);
 #pragma unroll
-                    for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+                    for (int j = 0; j < TN / 2; ++j) acc[i][j] = __ffma2_rn(aa, b[j], acc[i][j]);  // 2 FMAs / lane
                 }
             }
         }
@@ -140,7 +143,7 @@ __device__ __forceinline__ void gemm_tile(const GemmArgs &g, int bx, int by, int
         for (int j = 0; j < TN; ++j) {
             const int n = n0 + tx * TN + j;
             if (n >= g.N) continue;
-            float v = acc[i][j];
+            float v = (j & 1) ? acc[i][j >> 1].y : acc[i][j >> 1].x;
             if (g.bias) v += __ldg(g.bias + n);
             if (g.relu) v = fmaxf(v, 0.f);
             C[(size_t)m * g.ldc + n] = v;
@@ -232,7 +235,7 @@ __global__ void __launch_bounds__(256) fc_bwd_kernel(const FcBwdArgs a) {
     if (b < a.dg_n) {
         const int per_z = a.dg_gx * a.dg_gy;
         const int z = b / per_z, r = b - z * per_z;
-        gemm_tile<64, 32, 4, 2, true, false>(a.dg, r % a.dg_gx, r / a.dg_gx, z, As, Bs);
+        gemm_tile<64, 32, 2, 4, true, false>(a.dg, r % a.dg_gx, r / a.dg_gx, z, As, Bs);
         return;
     }
     b -= a.dg_n;
@@ -267,6 +270,7 @@ struct HeadArgs {
     unsigned *ticket;       // zero-initialised once; self-resetting
     float *stats_out;
     int B, nsplit, want_correct;
+    int defer_reduce;       // 1: only write rows[]; a later kernel (reduce_rows_block) produces stats_out
     float inv_B, loss_scale;
 };
 
@@ -335,33 +339,43 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
         zs[t] = s + __ldg(a.b2 + t);
     }
     __syncthreads();
-    if (t == 0) {
-        float m = zs[0];
-        int am = 0;
+    if (warp == 0) {
+        // log_softmax + NLL + dz2 on 10 lanes of one warp (shuffle reductions)
+        const float z = lane < kClasses ? zs[lane] : -INFINITY;
+        float m = z;
 #pragma unroll
-        for (int j = 1; j < kClasses; ++j)
-            if (zs[j] > m) { m = zs[j]; am = j; }
-        float se = 0.f;
-#pragma unroll
-        for (int j = 0; j < kClasses; ++j) se += expf(zs[j] - m);
+        for (int o = 8; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
+        const unsigned at_max = __ballot_sync(0xffffffffu, lane < kClasses && z == m);
+        const int am = __ffs(at_max) - 1;  // first maximum, like torch.max
+        const float e = lane < kClasses ? expf(z - m) : 0.f;
+        const float se = warp_sum(e);
         const float lse = m + logf(se);
         const long long tg = a.target[b];
         const bool ok = tg >= 0 && tg < kClasses;
-        float nll = __int_as_float(0x7fc00000);  // NaN for an out-of-range target
-#pragma unroll
-        for (int j = 0; j < kClasses; ++j) {
-            const float lp = zs[j] - lse;
-            if (a.logp) a.logp[(size_t)b * kClasses + j] = lp;
-            if (ok && j == (int)tg) nll = -lp;
-            const float d = (expf(lp) - ((ok && j == (int)tg) ? 1.f : 0.f)) * a.inv_B;
-            dzs[j] = d;
-            if (a.dz2) a.dz2[(size_t)b * kClasses + j] = d;
+        if (lane < kClasses) {
+            const float lp = z - lse;
+            const bool hit = ok && lane == (int)tg;
+            if (a.logp) a.logp[(size_t)b * kClasses + lane] = lp;
+            const float d = (expf(lp) - (hit ? 1.f : 0.f)) * a.inv_B;
+            dzs[lane] = d;
+            if (a.dz2) a.dz2[(size_t)b * kClasses + lane] = d;
+            if (hit) a.rows[b] = -lp;
         }
-        a.rows[b] = nll;
-        if (a.want_correct) a.rows[a.B + b] = (ok && am == (int)tg) ? 1.f : 0.f;
-        __threadfence();
-        const unsigned tk = atomicAdd(a.ticket, 1u);
-        is_last = (tk == gridDim.x - 1);
+        if (lane == 0) {
+            if (!ok) a.rows[b] = __int_as_float(0x7fc00000);  // NaN for an out-of-range target
+            if (a.want_correct) a.rows[a.B + b] = (ok && am == (int)tg) ? 1.f : 0.f;
+        }
+        if (!a.defer_reduce) {
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) {
+                const unsigned tk = atomicAdd(a.ticket, 1u);
+                is_last = (tk == gridDim.x - 1);
+            }
+        } else if (lane == 0) {
+            is_last = false;
+        }
     }
     __syncthreads();
     if (a.dz1) {

@@ -13,17 +13,87 @@ __device__ __forceinline__ float reduce_partials(const GradSegments &segs, int i
             const GradSegment &sg = segs.seg[s];
             const int r = i - sg.off;
             if (r >= 0 && r < sg.n) {
-                return sum_partials<kMaxGradSplit>(sg.part + r, sg.nsplit, (size_t)sg.stride);
+                float v = sum_partials<32>(sg.part + r, min(sg.nsplit, 32), (size_t)sg.stride);
+                if (sg.nsplit > 32)
+                    v += sum_partials<32>(sg.part + (size_t)32 * sg.stride + r, sg.nsplit - 32, (size_t)sg.stride);
+                return v;
             }
         }
     }
     return fallback;
 }
 
+// Same for four consecutive flat indices i4..i4+3 (i4 % 4 == 0) with 128-bit loads: one memory
+// round trip for up to 32 partial rows.  Elements outside every segment keep `fb`.
+__device__ __forceinline__ float4 reduce_partials4(const GradSegments &segs, int i4, float4 fb) {
+#pragma unroll
+    for (int s = 0; s < 6; ++s) {
+        if (s < segs.count) {
+            const GradSegment &sg = segs.seg[s];
+            const int r = i4 - sg.off;   // segment offsets and partial strides are multiples of 4
+            if (r >= 0 && r < sg.n) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int s0 = 0; s0 < sg.nsplit; s0 += 32) {
+                    float4 v[32];
+#pragma unroll
+                    for (int k = 0; k < 32; ++k)
+                        v[k] = (s0 + k < sg.nsplit)
+                                   ? __ldcg(reinterpret_cast<const float4 *>(sg.part + (size_t)(s0 + k) * sg.stride + r))
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+                    float4 a = v[0];
+#pragma unroll
+                    for (int k = 1; k < 32; ++k) { a.x += v[k].x; a.y += v[k].y; a.z += v[k].z; a.w += v[k].w; }
+                    if (s0 == 0) acc = a;
+                    else { acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w; }
+                }
+                const int left = sg.n - r;  // >= 1; elements past the segment end are bucket padding
+                return make_float4(acc.x, left > 1 ? acc.y : fb.y, left > 2 ? acc.z : fb.z, left > 3 ? acc.w : fb.w);
+            }
+        }
+    }
+    return fb;
+}
+
+// Deterministic sum of the per-row losses written by head_kernel (and of the per-row "correct"
+// flags when want_correct), by one CTA of 256 threads: strided partial sums, then a fixed tree.
+__device__ __forceinline__ void reduce_rows_block(const float *rows, int B, float scale, int want_correct,
+                                                  float *stats_out) {
+    __shared__ float red[256], red2[256];
+    const int t = threadIdx.x;
+    float s = 0.f, c = 0.f;
+    for (int r = t; r < B; r += 256) {
+        s += __ldcg(rows + r);
+        if (want_correct) c += __ldcg(rows + B + r);
+    }
+    red[t] = s;
+    red2[t] = c;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (t < o) { red[t] += red[t + o]; red2[t] += red2[t + o]; }
+        __syncthreads();
+    }
+    if (t == 0) {
+        stats_out[0] = red[0] * scale;
+        if (want_correct) stats_out[1] = red2[0];
+    }
+}
+
+struct LossReduce {   // rows == nullptr: nothing to do
+    const float *rows;
+    float *out;
+    int B;
+    float scale;
+};
+
 // Writes the summed partials into the flat gradient bucket (the tensors that come out of
 // batch-split kernels); everything else in the bucket is already final.
-__global__ void __launch_bounds__(256) grad_finalize_kernel(float *__restrict__ grads, const GradSegments segs) {
+__global__ void __launch_bounds__(256)
+grad_finalize_kernel(float *__restrict__ grads, const GradSegments segs, const LossReduce lr) {
     // segments cover [0, kOffF1W) (conv tensors) and [kOffF2W, kFlatElems) (fc2): skip fc1.
+    if (blockIdx.x == gridDim.x - 1) {  // last block: the scalar loss from the per-row losses
+        if (lr.rows) reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
+        return;
+    }
     int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= kOffF1W) i += kOffF2W - kOffF1W;
     if (i >= kFlatElems) return;
@@ -40,7 +110,9 @@ __global__ void __launch_bounds__(256)
 reduce_partials_to_kernel(float *__restrict__ out, const float *__restrict__ part, int n, int nsplit, int stride) {
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
-    out[i] = sum_partials<kMaxGradSplit>(part + i, nsplit, (size_t)stride);
+    float v = sum_partials<32>(part + i, min(nsplit, 32), (size_t)stride);
+    if (nsplit > 32) v += sum_partials<32>(part + (size_t)32 * stride + i, nsplit - 32, (size_t)stride);
+    out[i] = v;
 }
 
 // One SGD+momentum step over a flat fp32 range, 4 elements per thread.  Rounding matches
@@ -55,10 +127,7 @@ sgd_momentum_kernel(float *__restrict__ p, float *__restrict__ g, float *__restr
     if (i4 + 3 < n) {
         float4 gv = *reinterpret_cast<const float4 *>(g + i4);
         if (FUSED_FINALIZE) {
-            gv.x = reduce_partials(segs, i4, gv.x);
-            gv.y = reduce_partials(segs, i4 + 1, gv.y);
-            gv.z = reduce_partials(segs, i4 + 2, gv.z);
-            gv.w = reduce_partials(segs, i4 + 3, gv.w);
+            gv = reduce_partials4(segs, i4, gv);
             *reinterpret_cast<float4 *>(g + i4) = gv;  // keep the bucket inspectable (p.grad)
         }
         float4 pv = *reinterpret_cast<const float4 *>(p + i4);
@@ -82,6 +151,61 @@ sgd_momentum_kernel(float *__restrict__ p, float *__restrict__ g, float *__restr
             m[i] = mi;
             p[i] = __fmaf_rn(mi, neg_lr, p[i]);
         }
+    }
+}
+
+// The whole end of a single-process training step in one launch (mnist.py:43 + the tail of :42):
+//   blocks [0, kFusedCovBlocks)   : the ~31 k bucket elements whose gradients arrive as batch-split
+//                                   partials (conv1, conv2, fc2): one element per thread, all partial
+//                                   loads in flight at once, summed in a fixed order, then the update;
+//   next kFusedFc1Blocks blocks   : fc1 (93 % of the bucket, gradient already final): float4 per thread;
+//   last block                    : the scalar loss from the per-row losses.
+constexpr int kFusedCovElems = kOffF1W + (kFlatElems - kOffF2W);           // 30,784
+constexpr int kFusedCovBlocks = (kFusedCovElems + 255) / 256;              // 121
+constexpr int kFusedFc1Blocks = ((kOffF2W - kOffF1W) / 4 + 255) / 256;     // 392
+
+__device__ __forceinline__ void sgd_update1(float *p, float *m, int i, float gi, float neg_lr, float mu, float scale,
+                                            int first_step) {
+    gi = __fmul_rn(gi, scale);
+    const float mi = first_step ? gi : __fadd_rn(__fmul_rn(m[i], mu), gi);
+    m[i] = mi;
+    p[i] = __fmaf_rn(mi, neg_lr, p[i]);
+}
+
+__global__ void __launch_bounds__(256)
+sgd_fused_kernel(float *__restrict__ p, float *__restrict__ g, float *__restrict__ m, float neg_lr, float mu,
+                 float grad_scale, int first_step, const GradSegments segs, const LossReduce lr) {
+    const int blk = blockIdx.x, t = threadIdx.x;
+    if (blk < kFusedCovBlocks) {
+        int i = blk * 256 + t;
+        if (i >= kFusedCovElems) return;
+        if (i >= kOffF1W) i += kOffF2W - kOffF1W;
+        const float pv = p[i];                       // issued before the partial loads complete
+        const float mv = first_step ? 0.f : m[i];
+        const float gi = reduce_partials(segs, i, g[i]);
+        g[i] = gi;                                   // keep the bucket inspectable (p.grad)
+        const float gs = __fmul_rn(gi, grad_scale);
+        const float mi = first_step ? gs : __fadd_rn(__fmul_rn(mv, mu), gs);
+        m[i] = mi;
+        p[i] = __fmaf_rn(mi, neg_lr, pv);
+    } else if (blk < kFusedCovBlocks + kFusedFc1Blocks) {
+        const int i4 = kOffF1W + ((blk - kFusedCovBlocks) * 256 + t) * 4;
+        if (i4 >= kOffF2W) return;
+        const float4 gv = *reinterpret_cast<const float4 *>(g + i4);
+        const float4 pv = *reinterpret_cast<const float4 *>(p + i4);
+        float4 mv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!first_step) mv = *reinterpret_cast<const float4 *>(m + i4);
+        float gs[4] = {gv.x, gv.y, gv.z, gv.w}, ms[4] = {mv.x, mv.y, mv.z, mv.w}, ps[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float gj = __fmul_rn(gs[j], grad_scale);
+            ms[j] = first_step ? gj : __fadd_rn(__fmul_rn(ms[j], mu), gj);
+            ps[j] = __fmaf_rn(ms[j], neg_lr, ps[j]);
+        }
+        *reinterpret_cast<float4 *>(m + i4) = make_float4(ms[0], ms[1], ms[2], ms[3]);
+        *reinterpret_cast<float4 *>(p + i4) = make_float4(ps[0], ps[1], ps[2], ps[3]);
+    } else if (lr.rows) {
+        reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
     }
 }
 
