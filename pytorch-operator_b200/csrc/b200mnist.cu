@@ -72,7 +72,7 @@ Plan make_plan(int B) {
     p.fc1_split = clampi(148 / (16 * gy), 1, 10);  // 16 n-tiles x gy m-tiles x split <= one wave of 148 SMs
     p.fc1_kchunk = ceil_div(ceil_div(800, p.fc1_split), kGemmBK) * kGemmBK;
     p.fc1_split = ceil_div(800, p.fc1_kchunk);
-    p.dg_split = clampi(ceil_div(50, 25 * gy), 1, 8);
+    p.dg_split = clampi(ceil_div(100, 25 * gy), 1, 8);
     p.dg_kchunk = ceil_div(ceil_div(500, p.dg_split), kGemmBK) * kGemmBK;
     p.dg_split = ceil_div(500, p.dg_kchunk);
     p.fc2w_split = clampi(ceil_div(B, 16), 1, 32);
@@ -80,7 +80,8 @@ Plan make_plan(int B) {
     p.fc2w_split = ceil_div(B, p.fc2w_rows);
     p.c2w_split = clampi(ceil_div(B, 2), 1, 32);
     p.c1w_split = clampi(B, 1, kMaxGradSplit);
-    p.c2dg_gx = clampi(B, 1, 60);
+    // conv2 backward runs 2 CTAs/SM: 5*c2w_split weight-gradient CTAs + 5*c2dg_gx data-gradient CTAs <= 296
+    p.c2dg_gx = clampi(B, 1, (296 - 5 * p.c2w_split) / 5);
     return p;
 }
 

@@ -14,35 +14,42 @@ constexpr int kMaxDgSplit = 8;  // fc1 data-gradient split-K upper bound (dp2 pa
 // All global loads of a thread (<= 4 elements x (nsplit + 2)) are issued before any is used.
 //   PAIRED: rows hold the channel pair {r, r+25} interleaved -- D_s[r*ld + 2*pos + (oc >= 25)] -- so a
 //   128-bit load yields two ready-made (d[oc], d[oc+25]) operand pairs for FFMA2.
-template <int NTHREADS, bool PAIRED = false>
-__device__ __forceinline__ void scatter_dconv2(float *D_s, int ld, const float *__restrict__ dp2, int nsplit,
-                                               size_t split_stride, const float *__restrict__ p2,
-                                               const uint8_t *__restrict__ i2, size_t b, int tid) {
-    constexpr int PER = (kP2Elems + NTHREADS - 1) / NTHREADS;
+// Split in two so the global loads can be issued early (before a zero-fill / during the previous
+// image's math) and only the shared-memory stores sit behind the barrier.
+template <int NTHREADS>
+struct DConv2Regs {
+    static constexpr int PER = (kP2Elems + NTHREADS - 1) / NTHREADS;
     float g[PER], pv[PER];
     int q[PER];
+    __device__ __forceinline__ void load(const float *__restrict__ dp2, int nsplit, size_t split_stride,
+                                         const float *__restrict__ p2, const uint8_t *__restrict__ i2, size_t b,
+                                         int tid) {
 #pragma unroll
-    for (int j = 0; j < PER; ++j) {
-        const int e = tid + j * NTHREADS;
-        g[j] = 0.f; pv[j] = 0.f; q[j] = 0;
-        if (e < kP2Elems) {
-            const size_t o = b * kP2Elems + e;
-            pv[j] = __ldcg(p2 + o);
-            q[j] = i2[o];
-            g[j] = sum_partials<kMaxDgSplit>(dp2 + o, nsplit, split_stride);
+        for (int j = 0; j < PER; ++j) {
+            const int e = tid + j * NTHREADS;
+            g[j] = 0.f; pv[j] = 0.f; q[j] = 0;
+            if (e < kP2Elems) {
+                const size_t o = b * kP2Elems + e;
+                pv[j] = __ldcg(p2 + o);
+                q[j] = i2[o];
+                g[j] = sum_partials<kMaxDgSplit>(dp2 + o, nsplit, split_stride);
+            }
         }
     }
+    template <bool PAIRED>
+    __device__ __forceinline__ void store(float *D_s, int ld, int tid) const {
 #pragma unroll
-    for (int j = 0; j < PER; ++j) {
-        const int e = tid + j * NTHREADS;
-        if (e < kP2Elems && pv[j] > 0.f) {
-            const int oc = e >> 4, p = e & 15;
-            const int oy = 2 * (p >> 2) + (q[j] >> 1), ox = 2 * (p & 3) + (q[j] & 1);
-            if (PAIRED) D_s[(oc >= 25 ? oc - 25 : oc) * ld + 2 * (oy * 8 + ox) + (oc >= 25 ? 1 : 0)] = g[j];
-            else D_s[oc * ld + oy * 8 + ox] = g[j];
+        for (int j = 0; j < PER; ++j) {
+            const int e = tid + j * NTHREADS;
+            if (e < kP2Elems && pv[j] > 0.f) {
+                const int oc = e >> 4, p = e & 15;
+                const int oy = 2 * (p >> 2) + (q[j] >> 1), ox = 2 * (p & 3) + (q[j] & 1);
+                if (PAIRED) D_s[(oc >= 25 ? oc - 25 : oc) * ld + 2 * (oy * 8 + ox) + (oc >= 25 ? 1 : 0)] = g[j];
+                else D_s[oc * ld + oy * 8 + ox] = g[j];
+            }
         }
     }
-}
+};
 
 // ---------------------------------------------------------------------------------
 // conv2 data gradient as GEMM + col2im, per image and per tile of 4 input channels:
@@ -86,11 +93,14 @@ __device__ __forceinline__ void conv2_dgrad_tile(float *smem, const float *__res
         }
     }
     const int tm = tid >> 3, tn = tid & 7;  // tm < 25 active: rows 4*tm..+3; cols 4*tn..+3 and 32+4*tn..+3
+    DConv2Regs<kConvBwdThreads> dr;
+    if (vx < B) dr.load(dp2, nsplit, split_stride, p2, i2, (size_t)vx, tid);
     for (int b = vx; b < B; b += gx) {
         for (int i = tid; i < 50 * 64 / 4; i += kConvBwdThreads)
             reinterpret_cast<float4 *>(D_s)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncthreads();  // also orders W_s (first trip) and the previous trip's T_s readers
-        scatter_dconv2<kConvBwdThreads>(D_s, 64, dp2, nsplit, split_stride, p2, i2, (size_t)b, tid);
+        dr.template store<false>(D_s, 64, tid);
+        if (b + gx < B) dr.load(dp2, nsplit, split_stride, p2, i2, (size_t)(b + gx), tid);  // next image, in flight
         __syncthreads();
         if (tm < 25) {
             float2 acc[4][4];
@@ -184,6 +194,9 @@ __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__res
                     if (b < B) pv[j] = __ldg(reinterpret_cast<const float4 *>(p1 + (size_t)b * kP1Elems + ic0 * 144) + r);
                 }
             }
+            DConv2Regs<kConvBwdThreads> d0, d1;
+            d0.load(dp2, nsplit, split_stride, p2, i2, (size_t)bb, tid);
+            if (bb + 1 < B) d1.load(dp2, nsplit, split_stride, p2, i2, (size_t)bb + 1, tid);
             for (int i = tid; i < 2 * 25 * kWgLdD / 4; i += kConvBwdThreads)
                 reinterpret_cast<float4 *>(D_s)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -191,12 +204,10 @@ __device__ __forceinline__ void conv2_wgrad_tile(float *smem, const float *__res
                 const int i = tid + j * kConvBwdThreads;
                 if (i < 2 * kWgIcPerCta * 36) reinterpret_cast<float4 *>(P_s)[i] = pv[j];
             }
+            __syncthreads();
+            d0.template store<true>(D_s, kWgLdD, tid);
+            if (bb + 1 < B) d1.template store<true>(D_s + 25 * kWgLdD, kWgLdD, tid);
         }
-        __syncthreads();
-        scatter_dconv2<kConvBwdThreads, true>(D_s, kWgLdD, dp2, nsplit, split_stride, p2, i2, (size_t)bb, tid);
-        if (bb + 1 < B)
-            scatter_dconv2<kConvBwdThreads, true>(D_s + 25 * kWgLdD, kWgLdD, dp2, nsplit, split_stride, p2, i2,
-                                                  (size_t)bb + 1, tid);
         __syncthreads();
         if (active && bb + par < B) {
             const float *ps = P_s + (par * kWgIcPerCta + icl) * 144;
