@@ -277,6 +277,7 @@ def main():
 
     if rank != 0:
         if world > 1:
+            net.release_graphs()  # a graph holding NCCL kernels would make destroy_process_group() block
             dist.barrier()
             dist.destroy_process_group()
         return
@@ -360,6 +361,7 @@ def main():
     }
     print(json.dumps(line), flush=True)
     if world > 1:
+        net.release_graphs()
         dist.barrier()
         dist.destroy_process_group()
 

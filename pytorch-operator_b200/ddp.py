@@ -39,6 +39,9 @@ class DistributedDataParallel(nn.Module):
     def evaluate(self, *a, **k):
         return self.module.evaluate(*a, **k)
 
+    def release_graphs(self):
+        self.module.release_graphs()
+
     @property
     def device(self):
         return self.module.device

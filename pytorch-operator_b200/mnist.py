@@ -199,6 +199,8 @@ def main(argv=None):
             torch.save({k: v.detach().cpu().clone() for k, v in model.state_dict().items()}, "mnist_cnn.pt")
 
     if is_distributed():
+        model.release_graphs()  # graphs that captured NCCL kernels must go before the process group
+        getattr(model, "_b200_step_graphs", {}).clear()
         dist.barrier()
         dist.destroy_process_group()
 

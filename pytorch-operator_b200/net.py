@@ -66,6 +66,7 @@ class Net(nn.Module):
         self._ddp = None          # set by ddp.DistributedDataParallel
         self._ws = {}             # batch size -> workspace tensor
         self._loss = None
+        self._graphs = []         # weak refs to the StepGraphs captured on this model
         self._bind(flat, torch.zeros_like(flat), torch.zeros_like(flat))
 
     # ---- flat buckets and their named views -------------------------------------
@@ -89,6 +90,14 @@ class Net(nn.Module):
     @property
     def device(self):
         return self.flat_params.device
+
+    def release_graphs(self):
+        """Destroy every CUDA graph captured on this model (call before destroy_process_group())."""
+        for ref in self._graphs:
+            g = ref()
+            if g is not None:
+                g.release()
+        self._graphs = []
 
     def named_views(self, flat):
         return OrderedDict((name, flat[off:off + cnt].view(shape)) for name, shape, off, cnt in self._layout)
@@ -285,8 +294,18 @@ class StepGraph:
         for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum), saved):
             t.copy_(sv)
         torch.cuda.synchronize(dev)
-        with torch.cuda.graph(self.graph, stream=side):
+        # thread_local: the NCCL watchdog thread may query its own events while this thread captures
+        # (in the default global mode that query invalidates the capture and the ranks dead-lock)
+        with torch.cuda.graph(self.graph, stream=side, capture_error_mode="thread_local"):
             self.loss = model.train_step(self.x, self.target, optimizer)
+        model._graphs.append(weakref.ref(self))
+
+    def release(self):
+        """Destroy the captured graph.  A graph that captured NCCL kernels must be gone before
+        ``destroy_process_group()``, which otherwise blocks forever."""
+        if self.graph is not None:
+            self.graph.reset()
+            self.graph = None
 
     def replay(self):
         if (self.optimizer.lr, self.optimizer.momentum) != (self.lr, self.momentum):
