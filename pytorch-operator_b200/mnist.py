@@ -19,7 +19,7 @@ import torch
 import torch.distributed as dist
 
 from .ddp import DistributedDataParallel
-from .net import Net, StepGraph
+from .net import Net, StepPipeline
 from .optim import SGD
 
 try:  # mnist.py:6 imports tensorboardX unconditionally; it is optional here
@@ -39,7 +39,7 @@ WORLD_SIZE = int(os.environ.get('WORLD_SIZE', 1))
 
 def train(args, model, device, train_loader, optimizer, epoch, writer):
     """mnist.py:35-49.  Per batch: H2D copy, fused zero_grad/forward/nll_loss/backward/
-    all_reduce/step (CUDA-graph replay once the batch shape is known), and the same
+    all_reduce/step (double-buffered CUDA-graph replay once the batch shape is known), and the same
     ``loss.item()`` / print / add_scalar every ``log_interval`` batches."""
     model.train()
     graphs = getattr(model, "_b200_step_graphs", None)
@@ -50,11 +50,9 @@ def train(args, model, device, train_loader, optimizer, epoch, writer):
         B = len(data)
         g = graphs.get(B)
         if g is None and use_graph and not optimizer.first_step:
-            g = graphs[B] = StepGraph(model, optimizer, B)
+            g = graphs[B] = StepPipeline(model, optimizer, B)
         if g is not None:
-            g.x.copy_(data, non_blocking=True)
-            g.target.copy_(target, non_blocking=True)
-            loss = g.replay()
+            loss = g.submit(data, target)  # H2D on a copy stream, overlapped with the previous step
         else:
             data, target = data.to(device, non_blocking=True), target.to(device, non_blocking=True)
             loss = model.train_step(data, target, optimizer)

@@ -147,23 +147,26 @@ class Net(nn.Module):
         return logp
 
     # ---- fused entry points -----------------------------------------------------
-    def forward_backward(self, x, target, logp_out=None):
+    def forward_backward(self, x, target, logp_out=None, loss_out=None):
         """mnist.py:39-42 in one call: fills ``flat_grads`` (this rank's gradient) and returns
-        the mean-NLL loss as a 0-d device tensor (no sync)."""
+        the mean-NLL loss as a 0-d device tensor (no sync).  ``loss_out``: optional fp32 device
+        tensor (>= 1 element) to receive the loss instead of the model's own scalar."""
         x = self._check_inputs(x, target)
         B = x.shape[0]
         ws = self.workspace(B)
         L = _cabi.lib()
+        lo = self._loss if loss_out is None else loss_out
         _cabi.check(L.b200mnist_forward_backward(self.flat_params.data_ptr(), self.flat_grads.data_ptr(),
                                                  x.data_ptr(), target.data_ptr(), B, ws.data_ptr(), ws.numel(),
-                                                 self._loss.data_ptr(), _cabi.ptr(logp_out), _stream()),
+                                                 lo.data_ptr(), _cabi.ptr(logp_out), _stream()),
                     "forward_backward")
-        return self._loss[0]
+        return lo[0]
 
-    def train_step(self, x, target, optimizer):
+    def train_step(self, x, target, optimizer, loss_out=None):
         """mnist.py:39-43 in one call.  With DDP attached the gradient bucket is all-reduced
         between the backward and the update, and 1/world_size is folded into the update."""
         if self._ddp is None:
+            lo = self._loss if loss_out is None else loss_out
             x = self._check_inputs(x, target)
             B = x.shape[0]
             ws = self.workspace(B)
@@ -171,11 +174,11 @@ class Net(nn.Module):
             _cabi.check(L.b200mnist_train_step(self.flat_params.data_ptr(), self.flat_grads.data_ptr(),
                                                self.flat_momentum.data_ptr(), x.data_ptr(), target.data_ptr(), B,
                                                ws.data_ptr(), ws.numel(), optimizer.lr, optimizer.momentum,
-                                               1 if optimizer.first_step else 0, self._loss.data_ptr(), _stream()),
+                                               1 if optimizer.first_step else 0, lo.data_ptr(), _stream()),
                         "train_step")
             optimizer.first_step = False
-            return self._loss[0]
-        loss = self.forward_backward(x, target)
+            return lo[0]
+        loss = self.forward_backward(x, target, loss_out=loss_out)
         self._ddp.reduce_gradients()
         optimizer.step()
         return loss
@@ -269,7 +272,7 @@ class StepGraph:
     Static input buffers ``x``/``target`` are filled by the caller (e.g. an H2D copy) before
     ``replay()``; ``loss`` is a 0-d view of the device scalar the graph writes."""
 
-    def __init__(self, model: Net, optimizer, batch: int, x=None, target=None):
+    def __init__(self, model: Net, optimizer, batch: int, x=None, target=None, loss_out=None, loss_host=None):
         if optimizer.first_step:
             raise RuntimeError("run one eager step first (the first SGD step initialises the momentum buffer)")
         model = getattr(model, "module", model)  # accept our DistributedDataParallel wrapper
@@ -288,7 +291,7 @@ class StepGraph:
         # capture); it is a real step on zero data, so the training state is put back afterwards.
         saved = [t.clone() for t in (model.flat_params, model.flat_grads, model.flat_momentum)]
         with torch.cuda.stream(side):
-            model.train_step(self.x, self.target, optimizer)
+            model.train_step(self.x, self.target, optimizer, loss_out=loss_out)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize(dev)
         for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum), saved):
@@ -297,7 +300,10 @@ class StepGraph:
         # thread_local: the NCCL watchdog thread may query its own events while this thread captures
         # (in the default global mode that query invalidates the capture and the ranks dead-lock)
         with torch.cuda.graph(self.graph, stream=side, capture_error_mode="thread_local"):
-            self.loss = model.train_step(self.x, self.target, optimizer)
+            self.loss = model.train_step(self.x, self.target, optimizer, loss_out=loss_out)
+            if loss_host is not None:  # D2H memcpy node: every replay leaves the step's loss in pinned host memory
+                loss_host.copy_(self.loss.reshape(1), non_blocking=True)
+        self.loss_host = loss_host
         model._graphs.append(weakref.ref(self))
 
     def release(self):
@@ -312,3 +318,58 @@ class StepGraph:
             raise RuntimeError("lr/momentum changed after capture; build a new StepGraph")
         self.graph.replay()
         return self.loss
+
+
+class StepPipeline:
+    """Double-buffered host-fed training: while step i runs (graph replay on the current stream),
+    the pinned host batch of step i+1 is copied to the other static input buffer on a copy stream;
+    each replay ends with a D2H copy node that leaves the step's loss in pinned host memory.
+
+        pipe = StepPipeline(model, optimizer, batch)
+        for rec in pinned_records:          # uint8 [batch*784*4 + batch*8]: fp32 images, then int64 targets
+            loss_dev = pipe.submit(rec)     # asynchronous; loss_dev is a 0-d device tensor of that step
+        pipe.drain()                        # pipe.loss_host[k] holds the loss of the last step on slot k
+    """
+
+    def __init__(self, model, optimizer, batch: int):
+        net = getattr(model, "module", model)
+        dev = net.device
+        self.batch, self.xbytes, self.rec_bytes = batch, batch * 784 * 4, batch * 784 * 4 + batch * 8
+        self.slots = []
+        self.loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        for k in range(2):
+            packed = torch.zeros(self.rec_bytes, dtype=torch.uint8, device=dev)
+            x = packed[:self.xbytes].view(torch.float32).view(batch, 1, 28, 28)
+            t = packed[self.xbytes:].view(torch.int64)
+            loss_dev = torch.zeros(2, dtype=torch.float32, device=dev)
+            g = StepGraph(model, optimizer, batch, x=x, target=t, loss_out=loss_dev, loss_host=self.loss_host[k:k + 1])
+            self.slots.append((packed, g))
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.ev_copied = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ev_done = [torch.cuda.Event(), torch.cuda.Event()]
+        for e in self.ev_done:
+            e.record()
+        self.steps = 0
+
+    def submit(self, host_record, target=None):
+        """``host_record``: one packed uint8 record, or the image tensor when ``target`` is given."""
+        k = self.steps & 1
+        packed, g = self.slots[k]
+        main = torch.cuda.current_stream()
+        self.copy_stream.wait_event(self.ev_done[k])        # slot k's previous step has consumed its inputs
+        with torch.cuda.stream(self.copy_stream):           # H2D of this step's inputs, off the compute stream
+            if target is None:
+                packed.copy_(host_record, non_blocking=True)
+            else:
+                g.x.copy_(host_record, non_blocking=True)
+                g.target.copy_(target, non_blocking=True)
+            self.ev_copied[k].record(self.copy_stream)
+        main.wait_event(self.ev_copied[k])
+        loss = g.replay()
+        self.ev_done[k].record(main)
+        self.steps += 1
+        return loss
+
+    def drain(self):
+        torch.cuda.current_stream().synchronize()
+        self.copy_stream.synchronize()
