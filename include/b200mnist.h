@@ -100,6 +100,10 @@ int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *
 int64_t b200mnist_fc1_scratch_bytes(int B);
 int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, float *out, int B, void *scratch,
                            void *stream);
+/* The same F.relu(fc1(x)) (mnist.py:31) forced onto the tensor-core path: TMA-fed tcgen05.mma kind::tf32 with
+ * the 3xTF32 error-compensated split (fp32-level accuracy), accumulator in TMEM.  b200mnist_fc1_relu_fwd and the
+ * fused step pick it automatically for B >= 1024; this entry point exists so it can be tested at any B. */
+int b200mnist_fc1_relu_fwd_tc(const float *in, const float *w, const float *bias, float *out, int B, void *stream);
 /* F.log_softmax(fc2(h), dim=1) and F.nll_loss (mean), mnist.py:32-33,41, plus the start of
  * loss.backward() (mnist.py:42): dz2 = (softmax - onehot)/B and dz1 = (dz2 . W2) * (h > 0).
  * h [B,500]; logp [B,10]; dz2 [B,10]; dz1 [B,500] (NULL to skip the backward part);

@@ -11,6 +11,7 @@
 #include "conv_fwd.cuh"
 #include "fc.cuh"
 #include "optim.cuh"
+#include "tc_gemm.cuh"
 
 using namespace b200mnist;
 
@@ -148,9 +149,32 @@ int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out
     CHECK_LAUNCH("conv2_relu_pool_fwd", s);
     return 0;
 }
+// fc1 forward on the tensor cores (tcgen05 3xTF32, TMA-fed): large batches only.
+constexpr int kTcMinBatch = 1024;
+int launch_fc1_fwd_tc(const float *in, const float *w, const float *bias, float *h, int B, cudaStream_t s) {
+    CUtensorMap map_a, map_b;
+    if (!tc::make_map_kmajor(&map_a, in, B, 800, 800, tc::kBM) || !tc::make_map_kmajor(&map_b, w, 500, 800, 800, tc::kBN))
+        return fail_arg(8, "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)");
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(tc::fc1_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             tc::kSmemBytes);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(fc1_fwd_tc)");
+        attr_done = true;
+    }
+    tc::Fc1FwdTcArgs a{bias, h, B, 500, 800, 500, 1};
+    tc::fc1_fwd_tc_kernel<<<dim3(ceil_div(500, tc::kBN), ceil_div(B, tc::kBM)), tc::kThreads, tc::kSmemBytes, s>>>(
+        map_a, map_b, a);
+    CHECK_LAUNCH("fc1 forward gemm (tcgen05 3xTF32)", s);
+    return 0;
+}
 // fc1 forward: returns the number of split-K partials left in `part` (0 = `h` is final).
 int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h, float *part, int B, const Plan &pl,
                    cudaStream_t s, int *nsplit_out) {
+    if (B >= kTcMinBatch) {
+        *nsplit_out = 0;
+        return launch_fc1_fwd_tc(in, w, bias, h, B, s);
+    }
     GemmArgs g{};
     g.A = in; g.B = w; g.M = B; g.N = 500; g.K = 800; g.lda = 800; g.ldb = 800; g.kchunk = pl.fc1_kchunk;
     if (pl.fc1_split == 1) {
@@ -381,6 +405,13 @@ int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, f
     pl.fc1_kchunk = 800;
     int nsplit = 0;
     return launch_fc1_fwd(in, w, bias, out, static_cast<float *>(scratch), B, pl, s, &nsplit);
+}
+
+int b200mnist_fc1_relu_fwd_tc(const float *in, const float *w, const float *bias, float *out, int B, void *stream) {
+    if (!in || !w || !bias || !out) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(in) || !aligned16(w)) return fail_arg(3, "in/w must be 16-byte aligned");
+    return launch_fc1_fwd_tc(in, w, bias, out, B, static_cast<cudaStream_t>(stream));
 }
 
 int b200mnist_fc2_logsoftmax_nll(const float *h, const float *w, const float *bias, const int64_t *target, int B,

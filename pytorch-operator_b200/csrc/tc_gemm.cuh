@@ -1,0 +1,269 @@
+// 5th-generation tensor-core GEMM for the fc1 layer at large batch (BASELINE config 5: B = 4096 / rank):
+//   C[M,N] = relu(A[M,K] . B[N,K]^T + bias)      A = activations [B,800], B = fc1.weight [500,800]
+// written directly against the sm_100a programming model: TMA (cp.async.bulk.tensor) stages 128-byte
+// swizzled K-major tiles, one elected thread issues tcgen05.mma kind::tf32 with the accumulator in
+// TMEM, tcgen05.commit signals mbarriers, tcgen05.ld brings the tile back for the epilogue.
+//
+// Precision: a single TF32 pass (10-bit mantissa) misses the 1e-5 parity bound by two orders of
+// magnitude, so the kernel does the error-compensated 3xTF32 product.  A warp-specialised
+// "splitter" group turns every fp32 tile that lands in shared memory into hi = x with the low 13
+// mantissa bits cleared (exactly a TF32 number, whatever rounding the MMA applies to its inputs) and
+// lo = x - hi (exact in fp32), in place / at the same offsets, so the swizzled layout TMA produced
+// is preserved without any address arithmetic.  D += A_lo.B_hi + A_hi.B_lo + A_hi.B_hi per k-slice.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2-5 = splitters, then epilogue (TMEM lane quarter = warp_id % 4).
+// Every mbarrier wait is bounded: a barrier that never completes traps instead of hanging the GPU.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace b200mnist {
+namespace tc {
+
+constexpr int kBM = 128, kBN = 64, kBK = 32;           // CTA tile; kBK fp32 = one 128-byte swizzle row
+constexpr int kStages = 4;
+constexpr int kThreads = 192;
+constexpr int kTileA = kBM * kBK * 4, kTileB = kBN * kBK * 4;            // 16,384 B and 8,192 B
+constexpr int kStageBytes = 2 * kTileA + 2 * kTileB;                      // hi + lo of both = 49,152 B
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kTmemCols = 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bounded wait: ~2 s worth of polling, then trap (a lost barrier must not hang the box).
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+                 : "memory");
+}
+// K-major, 128-byte swizzle shared-memory matrix descriptor (LBO = 1, SBO = 8 rows x 128 B, version 1).
+__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;                 // leading byte offset (unused for swizzled K-major): 1
+    d |= (uint64_t)(1024 >> 4) << 32;       // stride byte offset: next group of 8 rows
+    d |= (uint64_t)1 << 46;                 // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                 // layout: SWIZZLE_128B
+    return d;
+}
+// Instruction descriptor: D = F32, A = B = TF32, both K-major, M x N tile.
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+                 : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
+                   "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
+                   "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr)
+                 : "memory");
+}
+
+struct Fc1FwdTcArgs {
+    const float *bias;
+    float *C;
+    int M, N, K, ldc, relu;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+fc1_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                  const Fc1FwdTcArgs g) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // stage s: [A_hi | A_lo | B_hi | B_lo]; barriers after the last stage
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes);
+    uint64_t *raw_full = bars, *split_full = bars + kStages, *empty = bars + 2 * kStages, *acc_full = bars + 3 * kStages;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 3 * kStages + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * kBM, n0 = blockIdx.x * kBN;
+    const int nkb = (g.K + kBK - 1) / kBK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(smem_u32(&raw_full[s]), 1);
+            mbar_init(smem_u32(&split_full[s]), 128);
+            mbar_init(smem_u32(&empty[s]), 1);
+        }
+        mbar_init(smem_u32(acc_full), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % kStages, ph = (kb / kStages) & 1;
+                mbar_wait(smem_u32(&empty[s]), ph ^ 1);
+                uint8_t *st = smem + s * kStageBytes;
+                const uint32_t bar = smem_u32(&raw_full[s]);
+                mbar_arrive_expect_tx(bar, kTileA + kTileB);
+                tma_load_2d(smem_u32(st), &map_a, kb * kBK, m0, bar);                  // raw A -> A_hi buffer
+                tma_load_2d(smem_u32(st + 2 * kTileA), &map_b, kb * kBK, n0, bar);     // raw B -> B_hi buffer
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_tf32(kBM, kBN);
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % kStages, ph = (kb / kStages) & 1;
+                mbar_wait(smem_u32(&split_full[s]), ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a_hi = smem_u32(smem + s * kStageBytes), a_lo = a_hi + kTileA;
+                const uint32_t b_hi = a_hi + 2 * kTileA, b_lo = b_hi + kTileB;
+#pragma unroll
+                for (int kk = 0; kk < kBK / 8; ++kk) {
+                    const uint32_t off = kk * 32;  // 8 fp32 along K inside the 128-byte swizzle row
+                    const uint64_t dah = umma_desc_k_sw128(a_hi + off), dal = umma_desc_k_sw128(a_lo + off);
+                    const uint64_t dbh = umma_desc_k_sw128(b_hi + off), dbl = umma_desc_k_sw128(b_lo + off);
+                    umma_tf32(tmem_d, dal, dbh, idesc, (kb | kk) ? 1u : 0u);   // small terms first
+                    umma_tf32(tmem_d, dah, dbl, idesc, 1u);
+                    umma_tf32(tmem_d, dah, dbh, idesc, 1u);
+                }
+                umma_commit(smem_u32(&empty[s]));          // stage free once these MMAs have read it
+            }
+            umma_commit(smem_u32(acc_full));               // accumulator complete
+        }
+    } else {
+        // ===== splitters (warps 2-5, 128 threads), then epilogue =====
+        const int t = threadIdx.x - 64;
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % kStages, ph = (kb / kStages) & 1;
+            mbar_wait(smem_u32(&raw_full[s]), ph);
+            uint8_t *st = smem + s * kStageBytes;
+            uint4 *ah = reinterpret_cast<uint4 *>(st), *al = reinterpret_cast<uint4 *>(st + kTileA);
+            uint4 *bh = reinterpret_cast<uint4 *>(st + 2 * kTileA), *bl = reinterpret_cast<uint4 *>(st + 2 * kTileA + kTileB);
+            auto split = [](uint4 v, uint4 &hi, uint4 &lo) {
+                hi = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u);
+                lo.x = __float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x));
+                lo.y = __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y));
+                lo.z = __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z));
+                lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
+            };
+#pragma unroll
+            for (int j = 0; j < kTileA / 16 / 128; ++j) {
+                uint4 hi, lo;
+                split(ah[t + j * 128], hi, lo);
+                ah[t + j * 128] = hi;
+                al[t + j * 128] = lo;
+            }
+#pragma unroll
+            for (int j = 0; j < kTileB / 16 / 128; ++j) {
+                uint4 hi, lo;
+                split(bh[t + j * 128], hi, lo);
+                bh[t + j * 128] = hi;
+                bl[t + j * 128] = lo;
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the MMA (async proxy)
+            mbar_arrive(smem_u32(&split_full[s]));
+        }
+        // epilogue: TMEM -> registers -> bias, ReLU -> global.  A warp may only touch its own lane quarter.
+        mbar_wait(smem_u32(acc_full), 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int q = warp & 3;
+        const int row = m0 + q * 32 + lane;
+#pragma unroll
+        for (int c = 0; c < kBN / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + c * 32, r);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (row < g.M) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int n = n0 + c * 32 + j;
+                    if (n < g.N) {
+                        float v = __uint_as_float(r[j]);
+                        if (g.bias) v += __ldg(g.bias + n);
+                        if (g.relu) v = fmaxf(v, 0.f);
+                        g.C[(size_t)row * g.ldc + n] = v;
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(kTmemCols) : "memory");
+    }
+}
+
+// ---- host side: tensor maps through the driver entry point (no link-time dependency on libcuda) ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// Row-major fp32 matrix [rows][cols] (cols contiguous), box = box_rows x 32 floats, 128-byte swizzle.
+inline bool make_map_kmajor(CUtensorMap *m, const float *base, int rows, int cols, int ld, int box_rows) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace tc
+}  // namespace b200mnist

@@ -1,0 +1,34 @@
+"""The tcgen05 (5th-gen tensor core) 3xTF32 fc1 GEMM against a float64 reference: fp32-level accuracy
+(north_star tolerance 1e-5) despite TF32 inputs, including ragged M (batch not a multiple of 128) and the
+N tail (500 = 7 x 64 + 52)."""
+import pytest
+import torch
+
+from tests.helpers import RTOL, assert_close
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("B", [128, 1, 200, 1000, 4096])
+def test_fc1_tensor_core_path_matches_fp64(B):
+    from pytorch_operator_b200 import _cabi
+    L = _cabi.lib()
+    g = torch.Generator().manual_seed(40 + B)
+    x = torch.relu(torch.randn(B, 800, generator=g))          # like the pooled conv2 activations: >= 0, many zeros
+    w = (torch.rand(500, 800, generator=g) - 0.5) * 0.07      # fc1's default-init scale
+    b = (torch.rand(500, generator=g) - 0.5) * 0.07
+    xd, wd, bd = x.to(DEV), w.to(DEV), b.to(DEV)
+    out = torch.full((B, 500), 7.0, device=DEV)
+    _cabi.check(L.b200mnist_fc1_relu_fwd_tc(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), out.data_ptr(), B,
+                                            torch.cuda.current_stream().cuda_stream), "fc1 tc")
+    torch.cuda.synchronize()
+    ref = torch.relu(x.double() @ w.double().T + b.double())
+    assert_close(out.cpu().numpy(), ref.numpy(), rtol=RTOL, what=f"fc1 tcgen05 B={B}")
+    # and against the fp32 SIMT kernel (same tolerance)
+    out2 = torch.empty(B, 500, device=DEV)
+    sc = torch.zeros(int(L.b200mnist_fc1_scratch_bytes(B)), dtype=torch.uint8, device=DEV)
+    if B < 1024:  # b200mnist_fc1_relu_fwd itself switches to the tensor-core path from 1024 up
+        _cabi.check(L.b200mnist_fc1_relu_fwd(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), out2.data_ptr(), B,
+                                             sc.data_ptr(), torch.cuda.current_stream().cuda_stream), "fc1 simt")
+        assert_close(out.cpu().numpy(), out2.cpu().numpy(), rtol=RTOL, what="tcgen05 vs SIMT")
