@@ -80,7 +80,7 @@ Plan make_plan(int B) {
     p.fc2w_rows = ceil_div(B, p.fc2w_split);
     p.fc2w_split = ceil_div(B, p.fc2w_rows);
     p.c2w_split = clampi(ceil_div(B, 2), 1, 32);
-    p.c1w_split = clampi(B, 1, kMaxGradSplit);
+    p.c1w_split = clampi(B <= 64 ? B : B / 2, 1, kMaxGradSplit);  // small B: one image per CTA; large B: fill the GPU
     // conv2 backward runs 2 CTAs/SM: 5*c2w_split weight-gradient CTAs + 5*c2dg_gx data-gradient CTAs <= 296
     p.c2dg_gx = clampi(B, 1, (296 - 5 * p.c2w_split) / 5);
     return p;

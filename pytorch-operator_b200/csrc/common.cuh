@@ -35,7 +35,7 @@ __device__ __forceinline__ float sum_partials(const float *p, int nsplit, size_t
     for (int s = 1; s < MAX; ++s) acc += v[s];
     return acc;
 }
-constexpr int kMaxGradSplit = 64;  // upper bound of every batch-split weight-gradient kernel
+constexpr int kMaxGradSplit = 296;  // upper bound of every batch-split weight-gradient kernel (2 CTAs x 148 SMs)
 
 // One gradient tensor whose value is the sum of `nsplit` partial buffers
 // (part + s*stride, s < nsplit), landing at flat offset `off` .. off+n.

@@ -14,8 +14,8 @@ __device__ __forceinline__ float reduce_partials(const GradSegments &segs, int i
             const int r = i - sg.off;
             if (r >= 0 && r < sg.n) {
                 float v = sum_partials<32>(sg.part + r, min(sg.nsplit, 32), (size_t)sg.stride);
-                if (sg.nsplit > 32)
-                    v += sum_partials<32>(sg.part + (size_t)32 * sg.stride + r, sg.nsplit - 32, (size_t)sg.stride);
+                for (int s0 = 32; s0 < sg.nsplit; s0 += 32)
+                    v += sum_partials<32>(sg.part + (size_t)s0 * sg.stride + r, min(sg.nsplit - s0, 32), (size_t)sg.stride);
                 return v;
             }
         }
@@ -111,7 +111,8 @@ reduce_partials_to_kernel(float *__restrict__ out, const float *__restrict__ par
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
     float v = sum_partials<32>(part + i, min(nsplit, 32), (size_t)stride);
-    if (nsplit > 32) v += sum_partials<32>(part + (size_t)32 * stride + i, nsplit - 32, (size_t)stride);
+    for (int s0 = 32; s0 < nsplit; s0 += 32)
+        v += sum_partials<32>(part + (size_t)s0 * stride + i, min(nsplit - s0, 32), (size_t)stride);
     out[i] = v;
 }
 
