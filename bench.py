@@ -184,6 +184,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG"):  # keep stdout clean for the single JSON line
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     lib = pkg._cabi.lib()
 
@@ -355,6 +357,8 @@ def main():
                           "frac_of_hbm_peak": step_bytes / (step_us * 1e-6) / 1e9 / peaks["hbm_gbs"]},
         "kernel_us": {k: round(v, 3) for k, v in sorted(kern_us.items(), key=lambda kv: -kv[1])},
         "kernel_us_sum": round(sum(kern_us.values()), 3),
+        "ddp_exchange": (None if world == 1 else ("fused peer-memory all-reduce+SGD kernel (NVLink P2P, symmetric memory)"
+                                                  if model.fused else "NCCL all_reduce + SGD kernel")),
         "cpu_baseline": cpu,
         "final_loss": loss_final,
     }

@@ -85,6 +85,20 @@ int b200mnist_forward_eval(const float *params, const float *x, const int64_t *t
 int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, int64_t n, float lr, float mu,
                            float grad_scale, int first_step, void *stream);
 
+/* Replaces DDP's gradient all_reduce (mnist.py:135-138) AND optimizer.step() (mnist.py:43) with one kernel
+ * over NVLink peer memory: waits until every rank's gradient bucket is ready, reads all `world_size` buckets
+ * (P2P loads), sums them in rank order (bit-identical on every rank), writes the sum to grads_sum and applies
+ *   g = sum*grad_scale; buf = first_step ? g : mu*buf + g; p = p - lr*buf
+ * over the whole flat bucket (B200MNIST_FLAT_ELEMS), then waits until every peer has finished reading.
+ *   peer_grads_host[r]   : HOST array of world_size DEVICE pointers: rank r's gradient bucket as mapped in
+ *                          this process (symmetric memory / CUDA IPC); entry [rank] is this rank's own bucket
+ *   peer_signals_host[r] : same for each rank's signal pad (>= 64 uint32, zero-filled once)
+ *   state                : 2 uint32 of local device memory, zero-filled once (epoch counter, CTA ticket)
+ * Every rank must call it once per step; the call only enqueues work.  world_size in [2, 8]. */
+int b200mnist_allreduce_sgd(float *params, float *momentum, float *grads_sum, const float *const *peer_grads_host,
+                            uint32_t *const *peer_signals_host, int rank, int world_size, uint32_t *state,
+                            float lr, float mu, float grad_scale, int first_step, void *stream);
+
 /* ---- per-layer entry points (used by the autograd bridge and the unit tests) ------- */
 
 /* F.max_pool2d(F.relu(conv1(x)), 2, 2), mnist.py:26-27.  x [B,1,28,28], w [20,1,5,5],

@@ -11,6 +11,7 @@
 #include "conv_fwd.cuh"
 #include "fc.cuh"
 #include "optim.cuh"
+#include "peer_allreduce.cuh"
 #include "tc_gemm.cuh"
 
 using namespace b200mnist;
@@ -374,6 +375,31 @@ int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, i
         return fail_arg(3, "params/grads/momentum must be 16-byte aligned");
     return launch_sgd(params, const_cast<float *>(grads), momentum, n, lr, mu, grad_scale, first_step,
                       static_cast<cudaStream_t>(stream));
+}
+
+int b200mnist_allreduce_sgd(float *params, float *momentum, float *grads_sum, const float *const *peer_grads_host,
+                            uint32_t *const *peer_signals_host, int rank, int world_size, uint32_t *state,
+                            float lr, float mu, float grad_scale, int first_step, void *stream) {
+    if (!params || !momentum || !grads_sum || !peer_grads_host || !peer_signals_host || !state)
+        return fail_arg(1, "null pointer argument");
+    if (world_size < 2 || world_size > kMaxPeers || rank < 0 || rank >= world_size)
+        return fail_arg(2, "world_size must be in [2, 8] and rank in [0, world_size)");
+    PeerArgs pa{};
+    for (int r = 0; r < world_size; ++r) {
+        if (!peer_grads_host[r] || !peer_signals_host[r]) return fail_arg(1, "null peer pointer");
+        if (!aligned16(peer_grads_host[r])) return fail_arg(3, "peer gradient buckets must be 16-byte aligned");
+        pa.grads[r] = peer_grads_host[r];
+        pa.signals[r] = peer_signals_host[r];
+    }
+    if (!aligned16(params) || !aligned16(momentum) || !aligned16(grads_sum))
+        return fail_arg(3, "params/momentum/grads_sum must be 16-byte aligned");
+    pa.rank = rank;
+    pa.world = world_size;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    allreduce_sgd_kernel<<<ceil_div(kFlatElems, 1024), 256, 0, s>>>(pa, params, momentum, grads_sum, kFlatElems, -lr, mu, grad_scale,
+                                             first_step, state, state + 1);
+    CHECK_LAUNCH("peer-memory all-reduce + sgd", s);
+    return 0;
 }
 
 int b200mnist_conv1_relu_pool_fwd(const float *x, const float *w, const float *bias, float *out, uint8_t *idx, int B,

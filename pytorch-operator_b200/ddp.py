@@ -1,20 +1,31 @@
 """``DistributedDataParallel`` -- what the reference gets from
 ``nn.parallel.DistributedDataParallel`` / ``DistributedDataParallelCPU`` (mnist.py:135-138):
 rank 0's parameters are broadcast at construction and every backward leaves the cross-rank
-gradient in place.  Here the exchange is ONE all_reduce(SUM) of the flat gradient bucket
-(1.7 MB) on the process group (NCCL over NVLink/NVSwitch on the GPU box); the 1/world_size
-is folded into the fused SGD kernel (exact for power-of-two world sizes)."""
+gradient in place.  Two exchange paths, both over ONE flat 1.7 MB gradient bucket:
+
+* fused (default on one NVLink-connected box): the step's gradient is written into a
+  symmetric-memory bucket every peer has mapped, and ``b200mnist_allreduce_sgd`` -- one kernel --
+  reads all ranks' buckets over NVLink, sums them in rank order, and applies the SGD update with
+  1/world_size folded in (no NCCL call, no separate optimizer launch);
+* NCCL: ``all_reduce(SUM)`` of the bucket on the process group, then the fused SGD kernel with
+  ``grad_scale = 1/world_size`` (also what the autograd-bridge path and gloo/CPU host tests use).
+"""
 from __future__ import annotations
+
+import ctypes
 
 import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from .net import Net
+from . import _cabi
+from .net import Net, _stream
+
+_PAD_OFFSET_BYTES = 8192  # our flags live at the end of the 9 KiB signal pad, away from torch's own channels
 
 
 class DistributedDataParallel(nn.Module):
-    def __init__(self, module: Net, process_group=None):
+    def __init__(self, module: Net, process_group=None, fused=None):
         super().__init__()
         if not isinstance(module, Net):
             raise TypeError("this DistributedDataParallel wraps pytorch_operator_b200.Net only")
@@ -23,18 +34,64 @@ class DistributedDataParallel(nn.Module):
         self.module = module
         self.process_group = process_group
         self.world_size = dist.get_world_size(process_group)
+        self.rank = dist.get_rank(process_group)
         object.__setattr__(module, "_ddp", self)  # plain back-reference, not a registered sub-module (no cycle)
         dist.broadcast(module.flat_params, src=0, group=process_group)  # DDP ctor semantics
+        self.fused = False
+        self.fused_error = None
+        want = fused if fused is not None else True
+        if want and module.device.type == "cuda" and 2 <= self.world_size <= 8 \
+                and dist.get_backend(process_group) == "nccl":
+            try:
+                self._setup_fused()
+                self.fused = True
+            except Exception as e:  # no peer access / symmetric memory unavailable: NCCL path
+                self.fused_error = repr(e)
+                if fused:
+                    raise
+        # every rank must take the same path
+        flag = torch.tensor([1 if self.fused else 0], device=module.device if module.device.type == "cuda" else "cpu")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=process_group)
+        self.fused = bool(flag.item())
 
+    def _setup_fused(self):
+        import torch.distributed._symmetric_memory as symm
+        net, ws = self.module, self.world_size
+        group = self.process_group if self.process_group is not None else dist.group.WORLD
+        self._staging = symm.empty(net.flat_grads.numel(), dtype=torch.float32, device=net.device)
+        self._staging.zero_()
+        self._symm = symm.rendezvous(self._staging, group)
+        if int(getattr(self._symm, "signal_pad_size", 0)) < _PAD_OFFSET_BYTES + 256:
+            raise RuntimeError("signal pad too small")
+        self._peer_grads = (ctypes.c_void_p * ws)(*[int(p) for p in self._symm.buffer_ptrs])
+        self._peer_signals = (ctypes.c_void_p * ws)(*[int(p) + _PAD_OFFSET_BYTES for p in self._symm.signal_pad_ptrs])
+        self._state = torch.zeros(2, dtype=torch.int32, device=net.device)
+        torch.cuda.synchronize(net.device)
+        dist.barrier(group=self.process_group)
+
+    # ---- exchange paths ----
     def reduce_gradients(self):
-        """Sum the flat gradient bucket over all ranks, in place, on the current stream."""
+        """NCCL path: sum the flat gradient bucket over all ranks, in place, on the current stream."""
         dist.all_reduce(self.module.flat_grads, op=dist.ReduceOp.SUM, group=self.process_group)
+
+    def fused_allreduce_sgd(self, optimizer):
+        """Fused path: peers' staged gradients -> rank-ordered sum in flat_grads -> SGD update, one kernel."""
+        m = self.module
+        _cabi.check(_cabi.lib().b200mnist_allreduce_sgd(
+            m.flat_params.data_ptr(), m.flat_momentum.data_ptr(), m.flat_grads.data_ptr(), self._peer_grads,
+            self._peer_signals, self.rank, self.world_size, self._state.data_ptr(), optimizer.lr, optimizer.momentum,
+            1.0 / self.world_size, 1 if optimizer.first_step else 0, _stream()), "allreduce_sgd")
+        optimizer.first_step = False
+
+    @property
+    def staging(self):
+        return self._staging if self.fused else None
 
     def forward(self, x):
         return self.module(x)
 
-    def train_step(self, x, target, optimizer):
-        return self.module.train_step(x, target, optimizer)
+    def train_step(self, x, target, optimizer, loss_out=None):
+        return self.module.train_step(x, target, optimizer, loss_out=loss_out)
 
     def evaluate(self, *a, **k):
         return self.module.evaluate(*a, **k)

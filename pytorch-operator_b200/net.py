@@ -147,7 +147,7 @@ class Net(nn.Module):
         return logp
 
     # ---- fused entry points -----------------------------------------------------
-    def forward_backward(self, x, target, logp_out=None, loss_out=None):
+    def forward_backward(self, x, target, logp_out=None, loss_out=None, grads_out=None):
         """mnist.py:39-42 in one call: fills ``flat_grads`` (this rank's gradient) and returns
         the mean-NLL loss as a 0-d device tensor (no sync).  ``loss_out``: optional fp32 device
         tensor (>= 1 element) to receive the loss instead of the model's own scalar."""
@@ -156,7 +156,8 @@ class Net(nn.Module):
         ws = self.workspace(B)
         L = _cabi.lib()
         lo = self._loss if loss_out is None else loss_out
-        _cabi.check(L.b200mnist_forward_backward(self.flat_params.data_ptr(), self.flat_grads.data_ptr(),
+        gr = self.flat_grads if grads_out is None else grads_out  # e.g. DDP's symmetric staging bucket
+        _cabi.check(L.b200mnist_forward_backward(self.flat_params.data_ptr(), gr.data_ptr(),
                                                  x.data_ptr(), target.data_ptr(), B, ws.data_ptr(), ws.numel(),
                                                  lo.data_ptr(), _cabi.ptr(logp_out), _stream()),
                     "forward_backward")
@@ -178,6 +179,10 @@ class Net(nn.Module):
                         "train_step")
             optimizer.first_step = False
             return lo[0]
+        if self._ddp.fused:
+            loss = self.forward_backward(x, target, loss_out=loss_out, grads_out=self._ddp.staging)
+            self._ddp.fused_allreduce_sgd(optimizer)
+            return loss
         loss = self.forward_backward(x, target, loss_out=loss_out)
         self._ddp.reduce_gradients()
         optimizer.step()

@@ -19,7 +19,9 @@ from tests.helpers import RTOL, golden_batch, golden_tensor_check, load_golden
 def main():
     mode = sys.argv[1] if len(sys.argv) > 1 else "eager"
     rank, ws = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    dev = torch.device("cuda", 0)  # the launcher pins one GPU per process, like one pod
+    # NCCL modes: the launcher pins one GPU per process (CUDA_VISIBLE_DEVICES), like one pod -> device 0.
+    # fused modes: all GPUs stay visible (peer mapping needs distinct device ordinals) -> device = rank.
+    dev = torch.device("cuda", 0 if torch.cuda.device_count() == 1 else rank)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
     gold = load_golden("train_ws2_b64")
@@ -29,12 +31,13 @@ def main():
     if rank == 0:
         torch.manual_seed(1)
         net.load_named({k: v for k, v in pkg.Net().state_dict().items()})
-    model = pkg.DistributedDataParallel(net)
+    model = pkg.DistributedDataParallel(net, fused=mode.startswith("fused"))
+    assert model.fused == mode.startswith("fused"), model.fused_error
     opt = pkg.SGD(model.parameters(), lr=0.01, momentum=0.5)
     graph = None
     for s in range(int(gold["meta/nsteps"][0])):
         x, t = golden_batch(gold, 64, s, rank)
-        if mode == "graph" and s > 0:
+        if mode.endswith("graph") and s > 0:
             graph = graph or pkg.StepGraph(model, opt, 64)
             graph.x.copy_(x)
             graph.target.copy_(t)
