@@ -152,22 +152,45 @@ int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out
 }
 // fc1 forward on the tensor cores (tcgen05 3xTF32, TMA-fed): large batches only.
 constexpr int kTcMinBatch = 1024;
-int launch_fc1_fwd_tc(const float *in, const float *w, const float *bias, float *h, int B, cudaStream_t s) {
-    CUtensorMap map_a, map_b;
-    if (!tc::make_map_kmajor(&map_a, in, B, 800, 800, tc::kBM) || !tc::make_map_kmajor(&map_b, w, 500, 800, 800, tc::kBN))
-        return fail_arg(8, "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)");
-    static bool attr_done = false;
+template <bool A_MN, bool B_MN, int EPI>
+int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, const tc::TcGemmArgs &a, const char *what, cudaStream_t s) {
+    static bool attr_done = false;  // one per template instantiation
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(tc::fc1_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             tc::kSmemBytes);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(fc1_fwd_tc)");
+        cudaError_t e = cudaFuncSetAttribute(tc::gemm_tc_kernel<A_MN, B_MN, EPI>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBytes);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(gemm_tc)");
         attr_done = true;
     }
-    tc::Fc1FwdTcArgs a{bias, h, B, 500, 800, 500, 1};
-    tc::fc1_fwd_tc_kernel<<<dim3(ceil_div(500, tc::kBN), ceil_div(B, tc::kBM)), tc::kThreads, tc::kSmemBytes, s>>>(
-        map_a, map_b, a);
-    CHECK_LAUNCH("fc1 forward gemm (tcgen05 3xTF32)", s);
+    const int ncols = a.N + (EPI == tc::kEpiWgrad ? 1 : 0);  // wgrad carries one extra column (the bias gradient)
+    tc::gemm_tc_kernel<A_MN, B_MN, EPI><<<dim3(ceil_div(ncols, tc::kBN), ceil_div(a.M, tc::kBM)), tc::kThreads,
+                                         tc::kSmemBytes, s>>>(ma, mb, a);
+    CHECK_LAUNCH(what, s);
     return 0;
+}
+const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)";
+
+int launch_fc1_fwd_tc(const float *in, const float *w, const float *bias, float *h, int B, cudaStream_t s) {
+    CUtensorMap ma, mb;
+    if (!tc::make_map_kmajor(&ma, in, B, 800, 800, tc::kBM) || !tc::make_map_kmajor(&mb, w, 500, 800, 800, tc::kBN))
+        return fail_arg(8, kTmapErr);
+    tc::TcGemmArgs a{bias, h, nullptr, B, 500, 800, 500};
+    return launch_tc<false, false, tc::kEpiBiasRelu>(ma, mb, a, "fc1 forward gemm (tcgen05 3xTF32)", s);
+}
+// dp2[B,800] = dz1[B,500] . W1[500,800]
+int launch_fc1_dgrad_tc(const float *dz1, const float *w1, float *dp2, int B, cudaStream_t s) {
+    CUtensorMap ma, mb;
+    if (!tc::make_map_kmajor(&ma, dz1, B, 500, 500, tc::kBM) || !tc::make_map_mnmajor(&mb, w1, 500, 800, 800))
+        return fail_arg(8, kTmapErr);
+    tc::TcGemmArgs a{nullptr, dp2, nullptr, B, 800, 500, 800};
+    return launch_tc<false, true, tc::kEpiStore>(ma, mb, a, "fc1 dgrad gemm (tcgen05 3xTF32)", s);
+}
+// gW1[500,800] = dz1[B,500]^T . p2[B,800] ; gb1[500] = column sums of dz1
+int launch_fc1_wgrad_tc(const float *dz1, const float *p2, float *gw1, float *gb1, int B, cudaStream_t s) {
+    CUtensorMap ma, mb;
+    if (!tc::make_map_mnmajor(&ma, dz1, B, 500, 500) || !tc::make_map_mnmajor(&mb, p2, B, 800, 800))
+        return fail_arg(8, kTmapErr);
+    tc::TcGemmArgs a{nullptr, gw1, gb1, 500, 800, B, 800};
+    return launch_tc<true, true, tc::kEpiWgrad>(ma, mb, a, "fc1 wgrad gemm (tcgen05 3xTF32)", s);
 }
 // fc1 forward: returns the number of split-K partials left in `part` (0 = `h` is final).
 int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h, float *part, int B, const Plan &pl,
@@ -195,6 +218,7 @@ int launch_head(const HeadArgs &a, cudaStream_t s) {
 }
 int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
                   float *gw1, float *gb1, float *dp2_part, float *fc2w_part, const Plan &pl, cudaStream_t s) {
+    const bool use_tc = B >= kTcMinBatch && pl.dg_split == 1;  // large batch: both fc1 GEMMs on the tensor cores
     FcBwdArgs a{};
     GemmArgs &g = a.wg;  // gW1[n,k] = sum_b dz1[b,n] p2[b,k] ; gb1[n] = sum_b dz1[b,n]
     g.A = dz1; g.B = p2; g.C = gw1; g.rowsum = gb1;
@@ -209,6 +233,13 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
     a.dg_n = a.dg_gx * a.dg_gy * pl.dg_split;
     a.dz2 = dz2; a.h = h; a.fc2_part = fc2w_part; a.B = B; a.fc2_rows = pl.fc2w_rows;
     a.fc2_gx = ceil_div(500, kFc2wThreads);
+    if (use_tc) {
+        a.wg_n = 0;
+        a.dg_n = 0;  // the SIMT launch keeps only the (tiny) fc2 weight-gradient role
+        int rc = launch_fc1_wgrad_tc(dz1, p2, gw1, gb1, B, s);
+        if (rc) return rc;
+        if ((rc = launch_fc1_dgrad_tc(dz1, w1, dp2_part, B, s))) return rc;
+    }
     fc_bwd_kernel<<<a.wg_n + a.dg_n + a.fc2_gx * pl.fc2w_split, 256, 0, s>>>(a);
     CHECK_LAUNCH("fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)", s);
     return 0;

@@ -1,5 +1,7 @@
-// 5th-generation tensor-core GEMM for the fc1 layer at large batch (BASELINE config 5: B = 4096 / rank):
-//   C[M,N] = relu(A[M,K] . B[N,K]^T + bias)      A = activations [B,800], B = fc1.weight [500,800]
+// 5th-generation tensor-core GEMMs for the fc1 layer at large batch (BASELINE config 5: B = 4096 / rank):
+//   forward : h   [B,500]   = relu(p2 [B,800] . W1[500,800]^T + b1)      A K-major,  B K-major
+//   dgrad   : dp2 [B,800]   = dz1[B,500] . W1[500,800]                   A K-major,  B MN-major
+//   wgrad   : gW1 [500,800] = dz1[B,500]^T . p2[B,800], gb1 = colsum(dz1) A MN-major, B MN-major
 // written directly against the sm_100a programming model: TMA (cp.async.bulk.tensor) stages 128-byte
 // swizzled K-major tiles, one elected thread issues tcgen05.mma kind::tf32 with the accumulator in
 // TMEM, tcgen05.commit signals mbarriers, tcgen05.ld brings the tile back for the epilogue.
@@ -12,7 +14,10 @@
 // is preserved without any address arithmetic.  D += A_lo.B_hi + A_hi.B_lo + A_hi.B_hi per k-slice.
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
-// warps 2-5 = splitters, then epilogue (TMEM lane quarter = warp_id % 4).
+// warps 2-5 = splitters + epilogue (TMEM lane quarter = warp_id % 4).
+// Long reductions (wgrad: K = batch): the tensor core's fp32 accumulation error grows with the number
+// of chained MMAs, so every kDrain k-blocks the TMEM tile is folded into fp32 registers (round-to-nearest
+// adds) by the epilogue warps while the MMA continues into the second TMEM accumulator.
 // Every mbarrier wait is bounded: a barrier that never completes traps instead of hanging the GPU.
 #pragma once
 #include <cuda.h>
@@ -28,7 +33,10 @@ constexpr int kThreads = 192;
 constexpr int kTileA = kBM * kBK * 4, kTileB = kBN * kBK * 4;            // 16,384 B and 8,192 B
 constexpr int kStageBytes = 2 * kTileA + 2 * kTileB;                      // hi + lo of both = 49,152 B
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-constexpr int kTmemCols = 64;
+static_assert(3 * kStages * 8 + 4 * 8 + 8 <= 256, "barrier area");
+constexpr int kTmemCols = 128;        // two 64-column accumulators (ping-pong)
+constexpr int kDrain = 8;            // k-blocks (K = 256) accumulated in TMEM before the tile is folded into fp32 registers
+constexpr int kDrainLag = 2;         // the splitters fold group g while they are already 2 k-blocks into group g+1
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -70,9 +78,23 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t saddr) {
     d |= (uint64_t)2 << 61;                 // layout: SWIZZLE_128B
     return d;
 }
-// Instruction descriptor: D = F32, A = B = TF32, both K-major, M x N tile.
-__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// MN-major operand of 32-bit elements: the only layout the TF32 MMA accepts is the 128-byte swizzle with a
+// 32-BYTE atom (UMMA layout type 1, TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): rows of 128 B = 32 contiguous
+// M/N elements, the four 32-byte units of a row XOR-permuted by (k-row % 4); an atom is 4 k-rows (512 B, SBO);
+// 32-element chunks along M/N are `chunk_bytes` apart (LBO).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128_32b(uint32_t saddr, uint32_t chunk_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)((chunk_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)(512 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)1 << 61;
+    return d;
+}
+// Instruction descriptor: D = F32, A = B = TF32, M x N tile; a_mn / b_mn = 1 for an MN-major operand.
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N, int a_mn = 0, int b_mn = 0) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -96,24 +118,33 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
                  : "memory");
 }
 
-struct Fc1FwdTcArgs {
-    const float *bias;
-    float *C;
-    int M, N, K, ldc, relu;
+enum Epilogue { kEpiBiasRelu = 0, kEpiStore = 1, kEpiWgrad = 2 };
+
+struct TcGemmArgs {
+    const float *bias;   // kEpiBiasRelu: added per n
+    float *C;            // [M][ldc]
+    float *colsum;       // kEpiWgrad: colsum[m] = sum_k A(m,k), delivered through a column of ones injected at n == N
+    int M, N, K, ldc;
 };
 
+// A_MN / B_MN: operand is MN-major in global memory (its M / N index is the contiguous one).
+template <bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
-fc1_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                  const Fc1FwdTcArgs g) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               const TcGemmArgs g) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     // stage s: [A_hi | A_lo | B_hi | B_lo]; barriers after the last stage
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes);
-    uint64_t *raw_full = bars, *split_full = bars + kStages, *empty = bars + 2 * kStages, *acc_full = bars + 3 * kStages;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 3 * kStages + 1);
+    uint64_t *raw_full = bars, *split_full = bars + kStages, *empty = bars + 2 * kStages;
+    uint64_t *acc_full = bars + 3 * kStages, *acc_empty = bars + 3 * kStages + 2;   // [2] each
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 3 * kStages + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * kBM, n0 = blockIdx.x * kBN;
     const int nkb = (g.K + kBK - 1) / kBK;
+    const int ngroups = (nkb + kDrain - 1) / kDrain;
+    // wgrad: the CTA whose N tile contains column N (= 800) carries the injected column of ones
+    const bool ones_cta = (EPI == kEpiWgrad) && (g.N >= n0) && (g.N < n0 + kBN);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
@@ -121,7 +152,10 @@ fc1_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             mbar_init(smem_u32(&split_full[s]), 128);
             mbar_init(smem_u32(&empty[s]), 1);
         }
-        mbar_init(smem_u32(acc_full), 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(smem_u32(&acc_full[b]), 1);
+            mbar_init(smem_u32(&acc_empty[b]), 128);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -144,37 +178,80 @@ fc1_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 uint8_t *st = smem + s * kStageBytes;
                 const uint32_t bar = smem_u32(&raw_full[s]);
                 mbar_arrive_expect_tx(bar, kTileA + kTileB);
-                tma_load_2d(smem_u32(st), &map_a, kb * kBK, m0, bar);                  // raw A -> A_hi buffer
-                tma_load_2d(smem_u32(st + 2 * kTileA), &map_b, kb * kBK, n0, bar);     // raw B -> B_hi buffer
+                // raw fp32 tiles land in the *_hi buffers
+                if (A_MN) {
+#pragma unroll
+                    for (int c = 0; c < kBM / 32; ++c)  // [32 k-rows x 32 m] boxes, 4 KB each
+                        tma_load_2d(smem_u32(st + c * 4096), &map_a, m0 + 32 * c, kb * kBK, bar);
+                } else {
+                    tma_load_2d(smem_u32(st), &map_a, kb * kBK, m0, bar);
+                }
+                if (B_MN) {
+#pragma unroll
+                    for (int c = 0; c < kBN / 32; ++c)
+                        tma_load_2d(smem_u32(st + 2 * kTileA + c * 4096), &map_b, n0 + 32 * c, kb * kBK, bar);
+                } else {
+                    tma_load_2d(smem_u32(st + 2 * kTileA), &map_b, kb * kBK, n0, bar);
+                }
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_tf32(kBM, kBN);
+            constexpr uint32_t idesc = umma_idesc_tf32(kBM, kBN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             for (int kb = 0; kb < nkb; ++kb) {
                 const int s = kb % kStages, ph = (kb / kStages) & 1;
+                const int grp = kb / kDrain, buf = grp & 1, kin = kb % kDrain;
+                if (kin == 0 && grp >= 2) {   // this accumulator was last used by group grp-2: wait until it has been folded
+                    mbar_wait(smem_u32(&acc_empty[buf]), ((grp >> 1) - 1) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
+                const uint32_t tmem_acc = tmem_d + buf * kBN;
                 mbar_wait(smem_u32(&split_full[s]), ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t a_hi = smem_u32(smem + s * kStageBytes), a_lo = a_hi + kTileA;
                 const uint32_t b_hi = a_hi + 2 * kTileA, b_lo = b_hi + kTileB;
 #pragma unroll
                 for (int kk = 0; kk < kBK / 8; ++kk) {
-                    const uint32_t off = kk * 32;  // 8 fp32 along K inside the 128-byte swizzle row
-                    const uint64_t dah = umma_desc_k_sw128(a_hi + off), dal = umma_desc_k_sw128(a_lo + off);
-                    const uint64_t dbh = umma_desc_k_sw128(b_hi + off), dbl = umma_desc_k_sw128(b_lo + off);
-                    umma_tf32(tmem_d, dal, dbh, idesc, (kb | kk) ? 1u : 0u);   // small terms first
-                    umma_tf32(tmem_d, dah, dbl, idesc, 1u);
-                    umma_tf32(tmem_d, dah, dbh, idesc, 1u);
+                    // 8 fp32 along K: 32 B inside the swizzle row (K-major) / one 1024-B atom of 8 k-rows (MN-major)
+                    const uint32_t aoff = A_MN ? kk * 1024 : kk * 32, boff = B_MN ? kk * 1024 : kk * 32;
+                    const uint64_t dah = A_MN ? umma_desc_mn_sw128_32b(a_hi + aoff, 4096) : umma_desc_k_sw128(a_hi + aoff);
+                    const uint64_t dal = A_MN ? umma_desc_mn_sw128_32b(a_lo + aoff, 4096) : umma_desc_k_sw128(a_lo + aoff);
+                    const uint64_t dbh = B_MN ? umma_desc_mn_sw128_32b(b_hi + boff, 4096) : umma_desc_k_sw128(b_hi + boff);
+                    const uint64_t dbl = B_MN ? umma_desc_mn_sw128_32b(b_lo + boff, 4096) : umma_desc_k_sw128(b_lo + boff);
+                    umma_tf32(tmem_acc, dal, dbh, idesc, (kin | kk) ? 1u : 0u);   // small terms first
+                    umma_tf32(tmem_acc, dah, dbl, idesc, 1u);
+                    umma_tf32(tmem_acc, dah, dbh, idesc, 1u);
                 }
                 umma_commit(smem_u32(&empty[s]));          // stage free once these MMAs have read it
+                if (kin == kDrain - 1 || kb == nkb - 1) umma_commit(smem_u32(&acc_full[buf]));  // group complete
             }
-            umma_commit(smem_u32(acc_full));               // accumulator complete
         }
     } else {
         // ===== splitters (warps 2-5, 128 threads), then epilogue =====
         const int t = threadIdx.x - 64;
+        const int q = warp & 3;            // a warp may only touch its own TMEM lane quarter
+        float acc[kBN];
+#pragma unroll
+        for (int j = 0; j < kBN; ++j) acc[j] = 0.f;
+        auto drain = [&](int grp) {        // fold accumulator (grp & 1) into the fp32 registers, then hand it back
+            const int buf = grp & 1;
+            mbar_wait(smem_u32(&acc_full[buf]), (grp >> 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int c = 0; c < kBN / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + buf * kBN + c * 32, r);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc[c * 32 + j] += __uint_as_float(r[j]);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(smem_u32(&acc_empty[buf]));
+        };
+        int next_drain = 0;
         for (int kb = 0; kb < nkb; ++kb) {
+            if (next_drain < ngroups && kb >= (next_drain + 1) * kDrain + kDrainLag) drain(next_drain++);
             const int s = kb % kStages, ph = (kb / kStages) & 1;
             mbar_wait(smem_u32(&raw_full[s]), ph);
             uint8_t *st = smem + s * kStageBytes;
@@ -201,29 +278,30 @@ fc1_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 bh[t + j * 128] = hi;
                 bl[t + j * 128] = lo;
             }
+            if (ones_cta) asm volatile("bar.sync 1, 128;" ::: "memory");  // the split pass has rewritten every vector of B_hi
+            if (ones_cta && t < kBK) {
+                // column n == N of B (all zeros from the out-of-bounds TMA fill) := 1.0 for this k-block's rows:
+                // MN-major chunk c = (N - n0)/32, k-row t at t*128 B, 32-byte unit ((col/8) ^ (t % 4)), float col%8
+                const int col = g.N - n0, c = col >> 5, cc = col & 31;
+                float *row = reinterpret_cast<float *>(st + 2 * kTileA + c * 4096 + t * 128);
+                row[(((cc >> 3) ^ (t & 3)) << 3) + (cc & 7)] = (kb * kBK + t < g.K) ? 1.0f : 0.0f;
+            }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the MMA (async proxy)
             mbar_arrive(smem_u32(&split_full[s]));
         }
-        // epilogue: TMEM -> registers -> bias, ReLU -> global.  A warp may only touch its own lane quarter.
-        mbar_wait(smem_u32(acc_full), 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int q = warp & 3;
+        while (next_drain < ngroups) drain(next_drain++);
+        // epilogue: registers -> global
         const int row = m0 + q * 32 + lane;
+        if (row < g.M) {
 #pragma unroll
-        for (int c = 0; c < kBN / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + c * 32, r);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            if (row < g.M) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int n = n0 + c * 32 + j;
-                    if (n < g.N) {
-                        float v = __uint_as_float(r[j]);
-                        if (g.bias) v += __ldg(g.bias + n);
-                        if (g.relu) v = fmaxf(v, 0.f);
-                        g.C[(size_t)row * g.ldc + n] = v;
-                    }
+            for (int j = 0; j < kBN; ++j) {
+                const int n = n0 + j;
+                float v = acc[j];
+                if (n < g.N) {
+                    if (EPI == kEpiBiasRelu) v = fmaxf(v + __ldg(g.bias + n), 0.f);
+                    g.C[(size_t)row * g.ldc + n] = v;
+                } else if (EPI == kEpiWgrad && n == g.N) {
+                    g.colsum[row] = v;
                 }
             }
         }
@@ -262,6 +340,19 @@ inline bool make_map_kmajor(CUtensorMap *m, const float *base, int rows, int col
     const cuuint32_t estr[2] = {1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// Same matrix viewed as an MN-major operand: box = 32 rows (k) x 32 contiguous elements (m or n), 4 KB.
+inline bool make_map_mnmajor(CUtensorMap *m, const float *base, int rows, int cols, int ld) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {32, (cuuint32_t)kBK};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 

@@ -32,3 +32,31 @@ def test_fc1_tensor_core_path_matches_fp64(B):
         _cabi.check(L.b200mnist_fc1_relu_fwd(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), out2.data_ptr(), B,
                                              sc.data_ptr(), torch.cuda.current_stream().cuda_stream), "fc1 simt")
         assert_close(out.cpu().numpy(), out2.cpu().numpy(), rtol=RTOL, what="tcgen05 vs SIMT")
+
+
+@pytest.mark.parametrize("B", [1024, 1500, 4096])
+def test_fc_backward_tensor_core_path_matches_fp64(B):
+    """b200mnist_fc_bwd at B >= 1024: fc1 weight gradient (MN-major x MN-major, bias gradient through an injected
+    column of ones) and fc1 data gradient (K-major x MN-major) run on tcgen05 3xTF32; fc2 stays on the SIMT kernel."""
+    from pytorch_operator_b200 import _cabi
+    L = _cabi.lib()
+    g = torch.Generator().manual_seed(90 + B)
+    dz2 = (torch.randn(B, 10, generator=g) / B)
+    dz1 = (torch.randn(B, 500, generator=g) / B) * (torch.rand(B, 500, generator=g) > 0.5)   # ReLU-masked, like the step
+    h = torch.relu(torch.randn(B, 500, generator=g))
+    p2 = torch.relu(torch.randn(B, 800, generator=g))
+    w1 = (torch.rand(500, 800, generator=g) - 0.5) * 0.07
+    d = {k: v.to(DEV) for k, v in dict(dz2=dz2, dz1=dz1, h=h, p2=p2, w1=w1).items()}
+    out = {"gw2": torch.full((10, 500), 7.0, device=DEV), "gb2": torch.full((10,), 7.0, device=DEV),
+           "gw1": torch.full((500, 800), 7.0, device=DEV), "gb1": torch.full((500,), 7.0, device=DEV),
+           "dp2": torch.full((B, 800), 7.0, device=DEV)}
+    sc = torch.zeros(int(L.b200mnist_fc_bwd_scratch_bytes(B)), dtype=torch.uint8, device=DEV)
+    _cabi.check(L.b200mnist_fc_bwd(d["dz2"].data_ptr(), d["dz1"].data_ptr(), d["h"].data_ptr(), d["p2"].data_ptr(),
+                                   d["w1"].data_ptr(), B, out["gw2"].data_ptr(), out["gb2"].data_ptr(),
+                                   out["gw1"].data_ptr(), out["gb1"].data_ptr(), out["dp2"].data_ptr(), sc.data_ptr(),
+                                   torch.cuda.current_stream().cuda_stream), "fc_bwd")
+    torch.cuda.synchronize()
+    ref = {"gw2": dz2.double().T @ h.double(), "gb2": dz2.double().sum(0), "gw1": dz1.double().T @ p2.double(),
+           "gb1": dz1.double().sum(0), "dp2": dz1.double() @ w1.double()}
+    for k in ref:
+        assert_close(out[k].cpu().numpy(), ref[k].numpy(), rtol=RTOL, what=f"{k} (B={B})")
