@@ -136,15 +136,43 @@ def cpu_reference_run(batch, steps, warmup, budget_s, threads=None):
             "ms_per_step": 1e3 * dt / done, "steps": done}
 
 
+def cpu_reference_run_ddp(batch, steps, warmup, budget_s, world):
+    """The reference's CPU/gloo configuration (BASELINE configs[0] generalised to `world` ranks): `world` local
+    processes, DistributedDataParallel on gloo, host cores split evenly between the ranks."""
+    import tempfile
+
+    import torch
+    import torch.multiprocessing as mp
+    from oracle import mnist_oracle as mo
+    cores = os.cpu_count() or 1
+    threads = max(1, cores // world)
+    path = os.path.join(tempfile.mkdtemp(), "ddp_cpu.json")
+    port = 29700 + (os.getpid() % 200)
+    mp.spawn(mo.ddp_cpu_worker, args=(world, port, batch, steps, warmup, budget_s, threads, path), nprocs=world, join=True)
+    with open(path) as f:
+        r = json.load(f)
+    return {"value": r["value"], "unit": UNIT, "cores": threads * world, "kind": "port",
+            "sample": f"{r['steps']} DDP training steps, {world} gloo ranks x batch {batch} x {threads} threads "
+                      f"(reference train() body + DistributedDataParallel on torch {torch.__version__} CPU ops, "
+                      f"{cores} host cpus), {r['seconds']:.1f} s",
+            "ms_per_step": r["ms_per_step"], "steps": r["steps"]}
+
+
 def run_reference_arm(args, rank):
     if rank != 0:
         return
-    r = cpu_reference_run(args.batch, args.steps, max(args.warmup, 3), budget_s=150.0)
+    if args.gpus > 1:
+        r = cpu_reference_run_ddp(args.batch, args.steps, max(args.warmup, 3), budget_s=120.0, world=args.gpus)
+        how = f"reference CPU path: {args.gpus} gloo ranks with DistributedDataParallel, per-rank batch {args.batch}"
+    else:
+        r = cpu_reference_run(args.batch, args.steps, max(args.warmup, 3), budget_s=150.0)
+        how = "reference CPU path, single process"
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": r["steps"], "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"examples/mnist Net train step, batch {args.batch}, synthetic 1x28x28 "
-                                   f"(reference CPU path, single process; steps capped at 150 s)"},
+            "config": {"workload": f"examples/mnist Net DDP train step (BASELINE configs[{1 if args.gpus == 1 else 2}]), "
+                                   f"per-rank batch {args.batch}, synthetic 1x28x28", "global_batch": args.gpus * args.batch,
+                       "how": how + "; steps capped by a time budget"},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}

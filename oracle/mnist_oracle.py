@@ -204,3 +204,61 @@ class TorchCpuTrainer:
         loss.backward()
         self.opt.step()
         return loss.detach()
+
+
+class OracleNet(torch.nn.Module):
+    """Module form of the same network (layer names as in mnist.py:20-23) for the gloo/DDP CPU baseline."""
+
+    def __init__(self):
+        super().__init__()
+        self.conv1 = torch.nn.Conv2d(1, 20, 5, 1)
+        self.conv2 = torch.nn.Conv2d(20, 50, 5, 1)
+        self.fc1 = torch.nn.Linear(800, 500)
+        self.fc2 = torch.nn.Linear(500, 10)
+
+    def forward(self, x):
+        return forward(dict(self.named_parameters()), x)
+
+
+def ddp_cpu_worker(rank, world, port, batch, steps, warmup, budget_s, threads, result_path):
+    """One rank of the reference's CPU/gloo configuration (BASELINE.json configs[0]; mnist.py:116,136-140):
+    DistributedDataParallel on gloo, optim.SGD(lr=.01, momentum=.5), per-rank synthetic batches.  Rank 0
+    writes {value: global images/s, ...} as JSON to result_path."""
+    import json
+    import os
+    import time
+
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.set_num_threads(max(1, threads))
+    dist.init_process_group("gloo")
+    torch.manual_seed(1)
+    model = torch.nn.parallel.DistributedDataParallel(OracleNet())
+    opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.5)
+    ring = [synthetic_batch(batch, 1234 + rank + 97 * i) for i in range(16)]
+
+    def step(i):
+        x, t = ring[i % 16]
+        opt.zero_grad()
+        loss = F.nll_loss(model(x), t)
+        loss.backward()
+        opt.step()
+        return loss
+
+    t0 = time.perf_counter()
+    for i in range(max(warmup, 3)):
+        step(i)
+    per = torch.tensor([(time.perf_counter() - t0) / max(warmup, 3)])
+    dist.all_reduce(per, op=dist.ReduceOp.MAX)
+    n = int(max(1, min(steps, budget_s / float(per))))  # the same count on every rank
+    dist.barrier()
+    t0 = time.perf_counter()
+    for i in range(n):
+        step(i)
+    dist.barrier()
+    dt = time.perf_counter() - t0
+    if rank == 0:
+        with open(result_path, "w") as f:
+            json.dump({"value": world * batch * n / dt, "steps": n, "ms_per_step": 1e3 * dt / n, "seconds": dt,
+                       "threads_per_rank": max(1, threads), "world": world}, f)
+    dist.destroy_process_group()
