@@ -54,6 +54,31 @@ inline void note_launch(const char *where, cudaStream_t s) {
         note_launch(where, stream);                           \
     } while (0)
 
+// Launch with programmatic dependent launch (PDL): the grid may be scheduled while its predecessor on the
+// stream is still draining; the kernel itself blocks in pdl_wait() until the predecessor has completed and
+// flushed.  Hides the ~2 us launch-to-launch gap of each of the step's dependent kernels, also under CUDA-graph
+// replay (stream capture turns the attribute into programmatic graph edges).
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args &&...args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#define CHECK_PDL(call, where, stream)                        \
+    do {                                                      \
+        cudaError_t e_ = (call);                              \
+        if (e_ != cudaSuccess) return fail_cuda(e_, where);   \
+        note_launch(where, stream);                           \
+    } while (0)
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -139,15 +164,15 @@ int check_step_args(const void *params, const void *x, const void *target, int B
 
 // ---- launches of the individual stages ----
 int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out, uint8_t *idx, int B, cudaStream_t s) {
-    conv1_relu_pool_fwd_kernel<<<dim3(B, 20 / kC1ChPerCta), kC1Threads, 0, s>>>(x, w, b, out, idx, B);
-    CHECK_LAUNCH("conv1_relu_pool_fwd", s);
+    CHECK_PDL(launch_pdl(conv1_relu_pool_fwd_kernel, dim3(B, 20 / kC1ChPerCta), dim3(kC1Threads), 0, s, x, w, b, out, idx, B),
+              "conv1_relu_pool_fwd", s);
     return 0;
 }
 int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
                      cudaStream_t s) {
-    conv2_relu_pool_fwd_kernel<<<dim3(ceil_div(B, kC2ImgPerCta), 50 / kC2OcPerCta), kC2Threads, 0, s>>>(in, w, b, out,
-                                                                                                      idx, B);
-    CHECK_LAUNCH("conv2_relu_pool_fwd", s);
+    CHECK_PDL(launch_pdl(conv2_relu_pool_fwd_kernel, dim3(ceil_div(B, kC2ImgPerCta), 50 / kC2OcPerCta), dim3(kC2Threads),
+                         0, s, in, w, b, out, idx, B),
+              "conv2_relu_pool_fwd", s);
     return 0;
 }
 // fc1 forward on the tensor cores (tcgen05 3xTF32, TMA-fed): large batches only.
@@ -206,14 +231,14 @@ int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h,
     } else {
         g.C = part; g.ldc = 512;
     }
-    gemm_kernel<64, 32, 2, 4, true, true><<<dim3(ceil_div(500, 32), ceil_div(B, 64), pl.fc1_split), 256, 0, s>>>(g);
-    CHECK_LAUNCH("fc1 forward gemm", s);
+    CHECK_PDL(launch_pdl(gemm_kernel<64, 32, 2, 4, true, true>, dim3(ceil_div(500, 32), ceil_div(B, 64), pl.fc1_split),
+                         dim3(256), 0, s, g),
+              "fc1 forward gemm", s);
     *nsplit_out = pl.fc1_split == 1 ? 0 : pl.fc1_split;
     return 0;
 }
 int launch_head(const HeadArgs &a, cudaStream_t s) {
-    head_kernel<<<a.B, kHeadThreads, 0, s>>>(a);
-    CHECK_LAUNCH("fc2/log_softmax/nll head", s);
+    CHECK_PDL(launch_pdl(head_kernel, dim3(a.B), dim3(kHeadThreads), 0, s, a), "fc2/log_softmax/nll head", s);
     return 0;
 }
 int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
@@ -240,8 +265,8 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
         if (rc) return rc;
         if ((rc = launch_fc1_dgrad_tc(dz1, w1, dp2_part, B, s))) return rc;
     }
-    fc_bwd_kernel<<<a.wg_n + a.dg_n + a.fc2_gx * pl.fc2w_split, 256, 0, s>>>(a);
-    CHECK_LAUNCH("fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)", s);
+    CHECK_PDL(launch_pdl(fc_bwd_kernel, dim3(a.wg_n + a.dg_n + a.fc2_gx * pl.fc2w_split), dim3(256), 0, s, a),
+              "fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)", s);
     return 0;
 }
 int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const float *p2, const uint8_t *i2,
@@ -258,14 +283,14 @@ int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const fl
     a.dp2 = dp2; a.p2 = p2; a.p1 = p1; a.w = w; a.i2 = i2; a.dp1 = dp1; a.part = c2w_part;
     a.split_stride = split_stride; a.nsplit = nsplit; a.B = B;
     a.wg_gy = pl.c2w_split; a.n_wg = 5 * pl.c2w_split; a.dg_gx = pl.c2dg_gx;
-    conv2_bwd_kernel<<<a.n_wg + 5 * a.dg_gx, kConvBwdThreads, kConv2BwdSmemBytes, s>>>(a);
-    CHECK_LAUNCH("conv2 backward (wgrad + dgrad)", s);
+    CHECK_PDL(launch_pdl(conv2_bwd_kernel, dim3(a.n_wg + 5 * a.dg_gx), dim3(kConvBwdThreads), kConv2BwdSmemBytes, s, a),
+              "conv2 backward (wgrad + dgrad)", s);
     return 0;
 }
 int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
                      const Plan &pl, cudaStream_t s) {
-    conv1_wgrad_kernel<<<dim3(pl.c1w_split, 2), kC1wThreads, 0, s>>>(x, dp1, p1, i1, c1w_part, B);
-    CHECK_LAUNCH("conv1 wgrad", s);
+    CHECK_PDL(launch_pdl(conv1_wgrad_kernel, dim3(pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1, c1w_part, B),
+              "conv1 wgrad", s);
     return 0;
 }
 
@@ -287,8 +312,8 @@ GradSegments step_segments(const Workspace &w, const Plan &pl) {
 }
 int launch_finalize(float *grads, const GradSegments &segs, const LossReduce &lr, cudaStream_t s) {
     const int n = kFlatElems - (kOffF2W - kOffF1W);
-    grad_finalize_kernel<<<ceil_div(n, 256) + 1, 256, 0, s>>>(grads, segs, lr);
-    CHECK_LAUNCH("grad finalize", s);
+    CHECK_PDL(launch_pdl(grad_finalize_kernel, dim3(ceil_div(n, 256) + 1), dim3(256), 0, s, grads, segs, lr),
+              "grad finalize", s);
     return 0;
 }
 // out[i] = sum of the partials (used by the per-layer entry points)
@@ -306,8 +331,9 @@ int launch_sgd(float *p, float *g, float *m, int64_t n, float lr, float mu, floa
 }
 int launch_sgd_fused(float *p, float *g, float *m, float lr, float mu, float scale, int first,
                      const GradSegments &segs, const LossReduce &lrd, cudaStream_t s) {
-    sgd_fused_kernel<<<kFusedCovBlocks + kFusedFc1Blocks + 1, 256, 0, s>>>(p, g, m, -lr, mu, scale, first, segs, lrd);
-    CHECK_LAUNCH("sgd momentum", s);
+    CHECK_PDL(launch_pdl(sgd_fused_kernel, dim3(kFusedCovBlocks + kFusedFc1Blocks + 1), dim3(256), 0, s, p, g, m, -lr, mu,
+                         scale, first, segs, lrd),
+              "sgd momentum", s);
     return 0;
 }
 

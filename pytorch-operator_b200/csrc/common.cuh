@@ -15,6 +15,12 @@ constexpr int kTensorElems[kNumTensors] = {500, 20, 25000, 50, 400000, 500, 5000
 // Per-image activation sizes (floats).
 constexpr int kXElems = 784, kP1Elems = 2880, kP2Elems = 800, kHElems = 500, kClasses = 10;
 
+// Programmatic dependent launch, device side.  pdl_wait(): block until the preceding grid on the stream has
+// completed and its writes are visible (returns at once for a normal launch).  pdl_trigger(): allow the next
+// grid to be scheduled as soon as every CTA of this grid has got this far.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

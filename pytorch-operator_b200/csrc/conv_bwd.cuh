@@ -291,6 +291,8 @@ struct Conv2BwdArgs {
 constexpr int kConv2BwdSmemBytes = kDgSmemFloats * 4;  // 60,000 B dynamic (covers both roles)
 
 __global__ void __launch_bounds__(kConvBwdThreads) conv2_bwd_kernel(const Conv2BwdArgs a) {
+
+    pdl_wait();
     extern __shared__ __align__(16) float smem[];
     int b = blockIdx.x;
     if (b < a.n_wg) {
@@ -318,6 +320,8 @@ constexpr int kC1PartStride = 576;  // 500 weights @0, 20 biases @512
 __global__ void __launch_bounds__(kC1wThreads)
 conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
                    const uint8_t *__restrict__ i1, float *__restrict__ part, int B) {
+
+    pdl_wait();
     __shared__ __align__(16) float xs[kXElems];
     __shared__ __align__(8) float2 lst[10][160];
     const int tid = threadIdx.x, wid = tid >> 5, c = blockIdx.y * 10 + wid, lane = tid & 31;

@@ -21,6 +21,8 @@ constexpr int kC1Threads = 160;
 __global__ void __launch_bounds__(kC1Threads)
 conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ bias,
                            float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
+
+    pdl_wait();
     __shared__ __align__(16) float xs[kXElems];
     __shared__ __align__(16) float ws[25 * kC1ChPerCta];
     __shared__ float bs[kC1ChPerCta];
@@ -149,6 +151,8 @@ constexpr int kC2Threads = kC2Warps * 32;
 __global__ void __launch_bounds__(kC2Threads)
 conv2_relu_pool_fwd_kernel(const float *__restrict__ in, const float *__restrict__ w, const float *__restrict__ bias,
                            float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
+
+    pdl_wait();
     __shared__ __align__(16) float smem_c2[kC2ImgPerCta * kP1Elems + 500 * 12];  // 23,040 + 24,000 B
     float *in_s = smem_c2;                            // [2][20][144]
     float *w_s = smem_c2 + kC2ImgPerCta * kP1Elems;   // [500][12]

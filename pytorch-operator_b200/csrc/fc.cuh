@@ -153,6 +153,8 @@ __device__ __forceinline__ void gemm_tile(const GemmArgs &g, int bx, int by, int
 
 template <int BM, int BN, int TM, int TN, bool A_KCONTIG, bool B_KCONTIG>
 __global__ void __launch_bounds__((BM / TM) * (BN / TN)) gemm_kernel(const GemmArgs g) {
+
+    pdl_wait();
     __shared__ __align__(16) float As[kGemmBK * (BM + 4)];
     __shared__ __align__(16) float Bs[kGemmBK * (BN + 4)];
     gemm_tile<BM, BN, TM, TN, A_KCONTIG, B_KCONTIG>(g, blockIdx.x, blockIdx.y, blockIdx.z, As, Bs);
@@ -224,6 +226,8 @@ struct FcBwdArgs {
 };
 
 __global__ void __launch_bounds__(256) fc_bwd_kernel(const FcBwdArgs a) {
+
+    pdl_wait();
     __shared__ __align__(16) float As[kGemmBK * (64 + 4)];
     __shared__ __align__(16) float Bs[kGemmBK * (64 + 4)];
     int b = blockIdx.x;
@@ -275,6 +279,8 @@ struct HeadArgs {
 };
 
 __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
+
+    pdl_wait();
     __shared__ __align__(16) float w2s[kClasses * kHElems];  // 20,000 B
     __shared__ float hs[512];
     __shared__ float wred[kHeadThreads / 32][kClasses];

@@ -89,6 +89,8 @@ struct LossReduce {   // rows == nullptr: nothing to do
 // batch-split kernels); everything else in the bucket is already final.
 __global__ void __launch_bounds__(256)
 grad_finalize_kernel(float *__restrict__ grads, const GradSegments segs, const LossReduce lr) {
+
+    pdl_wait();
     // segments cover [0, kOffF1W) (conv tensors) and [kOffF2W, kFlatElems) (fc2): skip fc1.
     if (blockIdx.x == gridDim.x - 1) {  // last block: the scalar loss from the per-row losses
         if (lr.rows) reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
@@ -176,6 +178,8 @@ __device__ __forceinline__ void sgd_update1(float *p, float *m, int i, float gi,
 __global__ void __launch_bounds__(256)
 sgd_fused_kernel(float *__restrict__ p, float *__restrict__ g, float *__restrict__ m, float neg_lr, float mu,
                  float grad_scale, int first_step, const GradSegments segs, const LossReduce lr) {
+
+    pdl_wait();
     const int blk = blockIdx.x, t = threadIdx.x;
     if (blk < kFusedCovBlocks) {
         int i = blk * 256 + t;
