@@ -94,10 +94,23 @@ int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, i
  *                          this process (symmetric memory / CUDA IPC); entry [rank] is this rank's own bucket
  *   peer_signals_host[r] : same for each rank's signal pad (>= 64 uint32, zero-filled once)
  *   state                : 2 uint32 of local device memory, zero-filled once (epoch counter, CTA ticket)
- * Every rank must call it once per step; the call only enqueues work.  world_size in [2, 8]. */
+ * Element range: the whole bucket except [skip_begin, skip_end) -- or, with only_skipped != 0, exactly that
+ * range (both multiples of 4).  This lets a caller exchange fc1's gradient (93 % of the bucket, final as soon as
+ * the fc backward kernel has run) on a side stream while the conv backward is still computing, and the rest
+ * afterwards; the two calls must use different `state` words and different signal-pad regions.
+ * Every rank must make the same calls in the same order; a call only enqueues work.  world_size in [2, 8]. */
 int b200mnist_allreduce_sgd(float *params, float *momentum, float *grads_sum, const float *const *peer_grads_host,
                             uint32_t *const *peer_signals_host, int rank, int world_size, uint32_t *state,
-                            float lr, float mu, float grad_scale, int first_step, void *stream);
+                            float lr, float mu, float grad_scale, int first_step, int64_t skip_begin, int64_t skip_end,
+                            int only_skipped, void *stream);
+
+/* b200mnist_forward_backward in two calls, for overlapping the gradient exchange with the backward pass:
+ * phase 1 = forward, loss head and the fc backward (afterwards fc1.weight / fc1.bias gradients are final in
+ * `grads`); phase 2 = conv backward and the reduction of the remaining partial gradients (+ loss_out).
+ * Same arguments as b200mnist_forward_backward; phase 2 must follow phase 1 on the same workspace. */
+int b200mnist_forward_backward_phase(const float *params, float *grads, const float *x, const int64_t *target, int B,
+                                     void *workspace, int64_t workspace_bytes, float *loss_out, float *logp_out,
+                                     int phase, void *stream);
 
 /* ---- per-layer entry points (used by the autograd bridge and the unit tests) ------- */
 

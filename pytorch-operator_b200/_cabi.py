@@ -71,7 +71,8 @@ SIGNATURES = {
     "b200mnist_forward_eval": (_i32, [_c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _c_f]),
     "b200mnist_sgd_momentum": (_i32, [_c_f, _c_f, _c_f, _i64, _f32, _f32, _f32, _i32, _c_f]),
     "b200mnist_allreduce_sgd": (_i32, [_c_f, _c_f, _c_f, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
-                                       _i32, _i32, _c_f, _f32, _f32, _f32, _i32, _c_f]),
+                                       _i32, _i32, _c_f, _f32, _f32, _f32, _i32, _i64, _i64, _i32, _c_f]),
+    "b200mnist_forward_backward_phase": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv1_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv2_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_fc1_scratch_bytes": (_i64, [_i32]),

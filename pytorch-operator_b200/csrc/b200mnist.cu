@@ -340,8 +340,15 @@ int launch_sgd_fused(float *p, float *g, float *m, float lr, float mu, float sca
 // forward (+ optional backward up to the partial gradients)
 int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target, int B, const Workspace &w,
                 const Plan &pl, bool backward, float *logp_out, float *stats_out, float loss_scale, int want_correct,
-                cudaStream_t s) {
+                cudaStream_t s, int phase = 0) {
+    // phase 0: everything; 1: forward + head + fc backward (fc1 gradients final); 2: conv backward only
     int rc;
+    if (phase == 2) {
+        if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B,
+                                   w.dp1, w.c2w_part, pl, s)))
+            return rc;
+        return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
+    }
     if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s))) return rc;
     if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, s))) return rc;
     int nsplit = 0;
@@ -359,6 +366,7 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     if ((rc = launch_fc_bwd(w.dz2, w.dz1, w.h, w.p2, P + kOffF1W, B, G + kOffF1W, G + kOffF1B, w.dp2_part,
                             w.fc2w_part, pl, s)))
         return rc;
+    if (phase == 1) return 0;
     if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B, w.dp1,
                                w.c2w_part, pl, s)))
         return rc;
@@ -391,6 +399,23 @@ int b200mnist_forward_backward(const float *params, float *grads, const float *x
     const Workspace w = carve(workspace, B);
     if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, logp_out, loss_out, 1.0f / (float)B, 0, s)))
         return rc;
+    LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
+    return launch_finalize(grads, step_segments(w, pl), lrd, s);
+}
+
+int b200mnist_forward_backward_phase(const float *params, float *grads, const float *x, const int64_t *target, int B,
+                                     void *workspace, int64_t workspace_bytes, float *loss_out, float *logp_out,
+                                     int phase, void *stream) {
+    if (phase != 1 && phase != 2) return fail_arg(2, "phase must be 1 or 2");
+    int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
+    if (rc) return rc;
+    if (!grads || !loss_out || !aligned16(grads)) return fail_arg(5, "grads/loss_out null or grads unaligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const Plan pl = make_plan(B);
+    const Workspace w = carve(workspace, B);
+    if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, logp_out, loss_out, 1.0f / (float)B, 0, s, phase)))
+        return rc;
+    if (phase == 1) return 0;
     LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
     return launch_finalize(grads, step_segments(w, pl), lrd, s);
 }
@@ -436,7 +461,8 @@ int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, i
 
 int b200mnist_allreduce_sgd(float *params, float *momentum, float *grads_sum, const float *const *peer_grads_host,
                             uint32_t *const *peer_signals_host, int rank, int world_size, uint32_t *state,
-                            float lr, float mu, float grad_scale, int first_step, void *stream) {
+                            float lr, float mu, float grad_scale, int first_step, int64_t skip_begin, int64_t skip_end,
+                            int only_skipped, void *stream) {
     if (!params || !momentum || !grads_sum || !peer_grads_host || !peer_signals_host || !state)
         return fail_arg(1, "null pointer argument");
     if (world_size < 2 || world_size > kMaxPeers || rank < 0 || rank >= world_size)
@@ -450,11 +476,19 @@ int b200mnist_allreduce_sgd(float *params, float *momentum, float *grads_sum, co
     }
     if (!aligned16(params) || !aligned16(momentum) || !aligned16(grads_sum))
         return fail_arg(3, "params/momentum/grads_sum must be 16-byte aligned");
+    if (skip_begin < 0 || skip_end < skip_begin || skip_end > kFlatElems || (skip_begin & 3) || (skip_end & 3))
+        return fail_arg(2, "skip range must lie in the bucket and be a multiple of 4 elements");
     pa.rank = rank;
     pa.world = world_size;
+    // element range handled by this call: [skip_begin, skip_end) if only_skipped, else everything but that range
+    const int lo = only_skipped ? (int)skip_begin : 0;
+    const int n = only_skipped ? (int)skip_end : kFlatElems;
+    const int hole_lo = only_skipped ? n : (int)skip_begin, hole_hi = only_skipped ? n : (int)skip_end;
+    const int count = (n - lo) - (hole_hi - hole_lo);
+    if (count <= 0) return 0;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    allreduce_sgd_kernel<<<ceil_div(kFlatElems, 1024), 256, 0, s>>>(pa, params, momentum, grads_sum, kFlatElems, -lr, mu, grad_scale,
-                                             first_step, state, state + 1);
+    allreduce_sgd_kernel<<<ceil_div(count, 1024), 256, 0, s>>>(pa, params, momentum, grads_sum, lo, hole_lo, hole_hi, n,
+                                                               -lr, mu, grad_scale, first_step, state, state + 1);
     CHECK_LAUNCH("peer-memory all-reduce + sgd", s);
     return 0;
 }

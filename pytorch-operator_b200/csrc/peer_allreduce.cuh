@@ -47,13 +47,15 @@ __device__ __forceinline__ void spin_until(const unsigned *p, unsigned want) {
 // signal pad layout (u32): [0..7] "gradient ready" flags by source rank, [8..15] "done reading" flags.
 __global__ void __launch_bounds__(256)
 allreduce_sgd_kernel(const PeerArgs pa, float *__restrict__ p, float *__restrict__ m, float *__restrict__ gsum,
-                     int n, float neg_lr, float mu, float grad_scale, int first_step, unsigned *epoch_ctr,
-                     unsigned *ticket) {
+                     int lo, int hole_lo, int hole_hi, int n, float neg_lr, float mu, float grad_scale, int first_step,
+                     unsigned *epoch_ctr, unsigned *ticket) {
     __shared__ bool is_last;
     const unsigned epoch = *reinterpret_cast<volatile unsigned *>(epoch_ctr) + 1;  // bumped by the last CTA only
     const int t = threadIdx.x;
     unsigned *my_pad = pa.signals[pa.rank];
-    const int i4 = (blockIdx.x * 256 + t) * 4;   // one float4 per thread: a single NVLink round trip per CTA
+    // one float4 per thread (a single NVLink round trip per CTA) over [lo, n) minus the hole [hole_lo, hole_hi)
+    int i4 = lo + (blockIdx.x * 256 + t) * 4;
+    if (i4 >= hole_lo) i4 += hole_hi - hole_lo;
     const bool mine = i4 < n;
     // local operands first: their latency overlaps the barrier
     float4 pv = make_float4(0.f, 0.f, 0.f, 0.f), mv = pv, own = pv;

@@ -65,7 +65,12 @@ class DistributedDataParallel(nn.Module):
             raise RuntimeError("signal pad too small")
         self._peer_grads = (ctypes.c_void_p * ws)(*[int(p) for p in self._symm.buffer_ptrs])
         self._peer_signals = (ctypes.c_void_p * ws)(*[int(p) + _PAD_OFFSET_BYTES for p in self._symm.signal_pad_ptrs])
-        self._state = torch.zeros(2, dtype=torch.int32, device=net.device)
+        self._state = torch.zeros(4, dtype=torch.int32, device=net.device)   # two exchange instances x (epoch, ticket)
+        self._peer_signals_b = (ctypes.c_void_p * ws)(*[int(p) + _PAD_OFFSET_BYTES + 256 for p in self._symm.signal_pad_ptrs])
+        L = _cabi.lib()
+        self._fc1_range = (int(L.b200mnist_tensor_offset(4)), int(L.b200mnist_tensor_offset(6)))
+        self._side = torch.cuda.Stream(device=net.device)
+        self._ev_fc, self._ev_side = torch.cuda.Event(), torch.cuda.Event()
         torch.cuda.synchronize(net.device)
         dist.barrier(group=self.process_group)
 
@@ -74,14 +79,32 @@ class DistributedDataParallel(nn.Module):
         """NCCL path: sum the flat gradient bucket over all ranks, in place, on the current stream."""
         dist.all_reduce(self.module.flat_grads, op=dist.ReduceOp.SUM, group=self.process_group)
 
-    def fused_allreduce_sgd(self, optimizer):
-        """Fused path: peers' staged gradients -> rank-ordered sum in flat_grads -> SGD update, one kernel."""
+    def _allreduce_sgd(self, optimizer, signals, state_ptr, only_fc1):
         m = self.module
         _cabi.check(_cabi.lib().b200mnist_allreduce_sgd(
             m.flat_params.data_ptr(), m.flat_momentum.data_ptr(), m.flat_grads.data_ptr(), self._peer_grads,
-            self._peer_signals, self.rank, self.world_size, self._state.data_ptr(), optimizer.lr, optimizer.momentum,
-            1.0 / self.world_size, 1 if optimizer.first_step else 0, _stream()), "allreduce_sgd")
+            signals, self.rank, self.world_size, state_ptr, optimizer.lr, optimizer.momentum,
+            1.0 / self.world_size, 1 if optimizer.first_step else 0, self._fc1_range[0], self._fc1_range[1],
+            1 if only_fc1 else 0, _stream()), "allreduce_sgd")
+
+    def fused_train_step(self, x, target, optimizer, loss_out=None):
+        """Fused path.  The gradient is produced into the symmetric staging bucket in two phases; fc1's part
+        (93 % of the bucket, final after the fc backward kernel) is exchanged + applied by the peer-memory kernel
+        on a side stream WHILE the conv backward runs, the remainder right after it.  Peers' staged gradients ->
+        rank-ordered sum in flat_grads -> SGD update, 1/world_size folded in."""
+        net = self.module
+        cur = torch.cuda.current_stream()
+        net.forward_backward_phase(x, target, 1, self._staging, loss_out)
+        self._ev_fc.record(cur)
+        self._side.wait_event(self._ev_fc)
+        with torch.cuda.stream(self._side):
+            self._allreduce_sgd(optimizer, self._peer_signals, self._state.data_ptr(), only_fc1=True)
+            self._ev_side.record(self._side)
+        loss = net.forward_backward_phase(x, target, 2, self._staging, loss_out)
+        self._allreduce_sgd(optimizer, self._peer_signals_b, self._state.data_ptr() + 8, only_fc1=False)
+        cur.wait_event(self._ev_side)
         optimizer.first_step = False
+        return loss
 
     @property
     def staging(self):
