@@ -43,9 +43,22 @@ KERNEL_WORK = {
     "fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)": (805_000, 2000 * 2 + 3200 + 3200 + 2000 + 40, 3_220_000),
     "conv2 backward (wgrad + dgrad)": (3_200_000, 3200 + 3200 + 800 + 11520 + 11520, 200_200),
     "conv1 wgrad": (288_000, 3136 + 11520 + 11520 + 2880, 2080),
+    "fc1 forward gemm (tcgen05 3xTF32)": (400_000, 3200 + 2000, 1_602_000),
+    "fc1 dgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_600_000),
+    "fc1 wgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_602_000),
     "sgd momentum": (0, 0, 5 * PARAM_BYTES),
     "grad finalize": (0, 0, 2 * 31_080 * 4),
 }
+
+
+def load_traffic(batch):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of each kernel, from the committed ncu --set full
+    capture of this workload (profiles/r01_traffic.json, written by tools/ncu_traffic.py); None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            return json.load(f).get(f"batch{batch}", {})
+    except Exception:
+        return {}
 
 
 def load_peaks():
@@ -350,10 +363,13 @@ def main():
     else:
         roof = {"bound": "hbm", "achieved": nbytes / t_top / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s"}
     roof["frac"] = roof["achieved"] / roof["peak"]
-    roof.update({"traffic": None, "kernel": top, "kernel_us": kern_us[top], "peak_source": peaks["source"] +
+    roof.update({"traffic": load_traffic(B).get(top), "kernel": top, "kernel_us": kern_us[top], "peak_source": peaks["source"] +
                  " (MEASURED_PEAKS.json burst bf16 / copy bandwidth)", "algorithmic_flops_per_launch": flops,
                  "algorithmic_bytes_per_launch": nbytes,
-                 "note": "fp32 SIMT kernel (1e-5 parity rules out 1-pass TF32); fraction is of the bf16 tensor peak"})
+                 "note": ("tcgen05 3xTF32 kernel: algorithmic (fp32-equivalent) FLOPs, 3 MMA passes per product"
+                          if "tcgen05" in top else
+                          "fp32 SIMT (FFMA2) kernel -- 1e-5 parity rules out single-pass TF32/bf16 MMA; at this batch the "
+                          "kernel is latency/occupancy bound (see profiles/), so both roofline fractions are low by construction")})
     step_us = 1e3 * ms_total / K
     step_flops, step_bytes = FLOPS_PER_IMAGE * B, HBM_BYTES_PER_IMAGE * B + 8 * PARAM_BYTES
 
