@@ -122,6 +122,12 @@ int b200mnist_conv1_relu_pool_fwd(const float *x, const float *w, const float *b
  * out [B,50,4,4] (= the [B,800] view of mnist.py:30). */
 int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
                                   int B, void *stream);
+/* The same conv2 + ReLU + max-pool (mnist.py:28-29) as an implicit GEMM on the tensor cores: im2col rows built in
+ * shared memory, weight tiles by TMA, tcgen05.mma kind::tf32 with the 3xTF32 split, pooling in the epilogue.
+ * Experimental in round 1 (slower than the direct convolution; the fused step uses it only with
+ * B200MNIST_CONV2_TC=1 in the environment). */
+int b200mnist_conv2_relu_pool_fwd_tc(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
+                                     int B, void *stream);
 /* F.relu(fc1(x)), mnist.py:31.  in [B,800], w [500,800], out [B,500].  `scratch` must hold
  * b200mnist_fc1_scratch_bytes(B) bytes (split-K partial sums). */
 int64_t b200mnist_fc1_scratch_bytes(int B);

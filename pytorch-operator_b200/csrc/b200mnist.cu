@@ -2,6 +2,7 @@
 // Host code here only validates arguments, carves the caller's workspace and enqueues
 // kernels on the caller's stream: no allocation, no synchronisation, no retained state.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -13,6 +14,7 @@
 #include "optim.cuh"
 #include "peer_allreduce.cuh"
 #include "tc_gemm.cuh"
+#include "tc_conv.cuh"
 
 using namespace b200mnist;
 
@@ -168,8 +170,51 @@ int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out,
               "conv1_relu_pool_fwd", s);
     return 0;
 }
+const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)";
+// conv2 forward as an implicit GEMM on the tensor cores (tcgen05 3xTF32, im2col built in shared memory)
+template <int NT>
+int launch_conv2_fwd_tc_n(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
+                          cudaStream_t s) {
+    CUtensorMap mw;
+    if (!tc::make_map_kmajor(&mw, w, 50, 500, 500, NT)) return fail_arg(8, kTmapErr);
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(tc::conv2_fwd_tc_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             tc::cv_smem_bytes<NT>());
+        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(conv2_fwd_tc)");
+        attr_done = true;
+    }
+    tc::conv2_fwd_tc_kernel<NT><<<dim3(ceil_div(B, 2), 64 / NT), tc::kThreads, tc::cv_smem_bytes<NT>(), s>>>(
+        mw, in, b, out, idx, B);
+    CHECK_LAUNCH("conv2_relu_pool_fwd (tcgen05 3xTF32 implicit GEMM)", s);
+    return 0;
+}
+int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
+                        cudaStream_t s) {
+    // small batches: two CTAs (32 channels each) per image pair so that more SMs take part
+    return B <= 296 ? launch_conv2_fwd_tc_n<32>(in, w, b, out, idx, B, s)
+                    : launch_conv2_fwd_tc_n<64>(in, w, b, out, idx, B, s);
+}
+// The tensor-core conv2 forward is correct (tests/test_gpu_tc.py) but, in round 1, slower than the FFMA2 direct
+// convolution at every batch size (28.6 vs 14.1 us at B=64, 347 vs 242 us at B=4096: the weight-tile TMA is issued
+// only when its stage frees up, so its latency is exposed every k-block), so it is opt-in: B200MNIST_CONV2_TC=1.
+int g_conv2_tc = -1;
+bool conv2_tc_enabled() {
+    if (g_conv2_tc < 0) {
+        const char *e = getenv("B200MNIST_CONV2_TC");
+        g_conv2_tc = (e && e[0] == '1') ? 1 : 0;
+    }
+    return g_conv2_tc != 0;
+}
+int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
+                          cudaStream_t s);
 int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
                      cudaStream_t s) {
+    if (conv2_tc_enabled()) return launch_conv2_fwd_tc(in, w, b, out, idx, B, s);
+    return launch_conv2_fwd_simt(in, w, b, out, idx, B, s);
+}
+int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
+                          cudaStream_t s) {
     CHECK_PDL(launch_pdl(conv2_relu_pool_fwd_kernel, dim3(ceil_div(B, kC2ImgPerCta), 50 / kC2OcPerCta), dim3(kC2Threads),
                          0, s, in, w, b, out, idx, B),
               "conv2_relu_pool_fwd", s);
@@ -192,7 +237,6 @@ int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, const tc::TcGemmArgs
     CHECK_LAUNCH(what, s);
     return 0;
 }
-const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)";
 
 int launch_fc1_fwd_tc(const float *in, const float *w, const float *bias, float *h, int B, cudaStream_t s) {
     CUtensorMap ma, mb;
@@ -507,6 +551,14 @@ int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *
     if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
     if (!aligned16(in)) return fail_arg(3, "in must be 16-byte aligned");
     return launch_conv2_fwd(in, w, bias, out, idx, B, static_cast<cudaStream_t>(stream));
+}
+
+int b200mnist_conv2_relu_pool_fwd_tc(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
+                                     int B, void *stream) {
+    if (!in || !w || !bias || !out || !idx) return fail_arg(1, "null pointer argument");
+    if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
+    if (!aligned16(in) || !aligned16(w)) return fail_arg(3, "in/w must be 16-byte aligned");
+    return launch_conv2_fwd_tc(in, w, bias, out, idx, B, static_cast<cudaStream_t>(stream));
 }
 
 int64_t b200mnist_fc1_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)10 * B * 512 * 4; }

@@ -60,3 +60,35 @@ def test_fc_backward_tensor_core_path_matches_fp64(B):
            "gb1": dz1.double().sum(0), "dp2": dz1.double() @ w1.double()}
     for k in ref:
         assert_close(out[k].cpu().numpy(), ref[k].numpy(), rtol=RTOL, what=f"{k} (B={B})")
+
+
+@pytest.mark.parametrize("B", [1, 2, 63, 64, 300, 1000])
+def test_conv2_implicit_gemm_tensor_core_path_matches_oracle(B):
+    """conv2 + ReLU + pool as a tcgen05 implicit GEMM (im2col built in shared memory) against float64, and its
+    arg-max map against the fp32 SIMT kernel wherever the window maximum is not a near-tie."""
+    import numpy as np
+    import torch.nn.functional as F
+    from oracle import mnist_oracle as mo
+    from pytorch_operator_b200 import _cabi
+    L = _cabi.lib()
+    params = mo.init_params(1)
+    g = torch.Generator().manual_seed(70 + B)
+    p1 = torch.relu(torch.randn(B, 20, 12, 12, generator=g))
+    w, b = params["conv2.weight"], params["conv2.bias"]
+    d = {"p1": p1.to(DEV), "w": w.to(DEV), "b": b.to(DEV)}
+    outs = {}
+    for name, fn in (("tc", L.b200mnist_conv2_relu_pool_fwd_tc), ("simt", L.b200mnist_conv2_relu_pool_fwd)):
+        out = torch.full((B, 50, 4, 4), 7.0, device=DEV)
+        idx = torch.full((B, 50, 4, 4), 9, dtype=torch.uint8, device=DEV)
+        _cabi.check(fn(d["p1"].data_ptr(), d["w"].data_ptr(), d["b"].data_ptr(), out.data_ptr(), idx.data_ptr(), B,
+                       torch.cuda.current_stream().cuda_stream), name)
+        torch.cuda.synchronize()
+        outs[name] = (out.cpu(), idx.cpu())
+    c = F.relu(F.conv2d(p1.double(), w.double(), b.double()))
+    ref = F.max_pool2d(c, 2, 2)
+    assert_close(outs["tc"][0].numpy(), ref.numpy(), rtol=RTOL, what=f"p2 tcgen05 B={B}")
+    win = c.unfold(2, 2, 2).unfold(3, 2, 2).reshape(B, 50, 4, 4, 4)
+    top2 = win.topk(2, dim=-1).values
+    clear = ((top2[..., 0] - top2[..., 1]) > 1e-5) & (top2[..., 0] > 1e-5)
+    assert np.array_equal(outs["tc"][1].numpy()[clear.numpy()], win.argmax(-1).numpy()[clear.numpy()])
+    assert np.array_equal(outs["tc"][1].numpy()[clear.numpy()], outs["simt"][1].numpy()[clear.numpy()])
