@@ -389,7 +389,7 @@ def main():
                    "cuda_graph": True, "lr": 0.01, "momentum": 0.5},
         "e2e": {"value": world * B * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": rec,
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K,
-                "how": "StepPipeline.submit(pinned record): H2D on a copy stream into the idle one of two static buffers, graph replay, D2H copy node of the loss to pinned host memory -- every step"},
+                "how": "StepPipeline.submit(pinned record): H2D on a copy stream into the idle one of two static buffers, graph replay, the loss stored by the last kernel straight into pinned host memory (zero-copy D2H) -- every step"},
         "gpu_launches": kernels_per_step * K,
         "kernels_per_step": kernels_per_step,
         "clocks": clocks, "clocks_e2e": clocks_e2e,

@@ -184,6 +184,14 @@ int b200mnist_conv1_bwd(const float *dp1, const float *p1, const uint8_t *idx1, 
 /* The worker's op in examples/smoke-dist/dist_sendrecv.py:32, torch.mul(inp, inp). */
 int b200mnist_square(const float *in, float *out, int64_t n, void *stream);
 
+/* Host plumbing for `data.to(device)` (mnist.py:38) in a double-buffered pipeline: on `copy_stream` wait for
+ * ev_slot_free (cudaEvent_t: the step that last used this input slot is done), copy `bytes` from PINNED host
+ * memory to the device slot, record ev_copied; make `compute_stream` wait for ev_copied.  Enqueues only.
+ * b200mnist_event_record is cudaEventRecord(event, stream) (to mark a slot's step as done). */
+int b200mnist_stage_inputs(void *dst_device, const void *src_host_pinned, int64_t bytes, void *copy_stream,
+                           void *compute_stream, void *ev_slot_free, void *ev_copied);
+int b200mnist_event_record(void *event, void *stream);
+
 /* ---- instrumentation for bench.py (no counterpart in the reference) ----------------
  * b200mnist_launch_count: kernels this library has launched in this process so far.
  * b200mnist_profile_begin/end: while enabled, a CUDA event is recorded on `stream` after

@@ -89,6 +89,8 @@ SIGNATURES = {
     "b200mnist_conv1_bwd_scratch_bytes": (_i64, [_i32]),
     "b200mnist_conv1_bwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f, _c_f, _c_f]),
     "b200mnist_square": (_i32, [_c_f, _c_f, _i64, _c_f]),
+    "b200mnist_stage_inputs": (_i32, [_c_f, _c_f, _i64, _c_f, _c_f, _c_f, _c_f]),
+    "b200mnist_event_record": (_i32, [_c_f, _c_f]),
     "b200mnist_launch_count": (ctypes.c_longlong, []),
     "b200mnist_profile_begin": (_i32, [_c_f, _i32]),
     "b200mnist_profile_end": (_i32, [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), _i32, _c_f]),

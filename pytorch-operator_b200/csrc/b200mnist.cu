@@ -111,6 +111,22 @@ Plan make_plan(int B) {
     p.c1w_split = clampi(B <= 64 ? B : B / 2, 1, kMaxGradSplit);  // small B: one image per CTA; large B: fill the GPU
     // conv2 backward runs 2 CTAs/SM: 5*c2w_split weight-gradient CTAs + 5*c2dg_gx data-gradient CTAs <= 296
     p.c2dg_gx = clampi(B, 1, (296 - 5 * p.c2w_split) / 5);
+    // tuning overrides (development only): B200MNIST_PLAN="fc1_split,dg_split,c2w_split,c2dg_gx" (0 = keep)
+    static int ov[4] = {-1, 0, 0, 0};
+    if (ov[0] < 0) {
+        ov[0] = 0;
+        if (const char *e = getenv("B200MNIST_PLAN")) sscanf(e, "%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3]);
+    }
+    if (ov[0] > 0) {
+        p.fc1_kchunk = ceil_div(ceil_div(800, ov[0]), kGemmBK) * kGemmBK;
+        p.fc1_split = ceil_div(800, p.fc1_kchunk);
+    }
+    if (ov[1] > 0) {
+        p.dg_kchunk = ceil_div(ceil_div(500, ov[1]), kGemmBK) * kGemmBK;
+        p.dg_split = ceil_div(500, p.dg_kchunk);
+    }
+    if (ov[2] > 0) p.c2w_split = clampi(ov[2], 1, 32);
+    if (ov[3] > 0) p.c2dg_gx = clampi(ov[3], 1, B);
     return p;
 }
 
@@ -720,6 +736,28 @@ int b200mnist_square(const float *in, float *out, int64_t n, void *stream) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     square_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, out, (long long)n);
     CHECK_LAUNCH("square", s);
+    return 0;
+}
+
+/* ---- host-side plumbing for the double-buffered input pipeline (mnist.py:38, data.to(device)) ----
+ * One call = the four stream operations of StepPipeline.submit, without Python in between:
+ *   copy stream waits until the slot's previous step has finished (ev_slot_free), H2D copy of the record,
+ *   ev_copied recorded on the copy stream, compute stream waits for ev_copied. */
+int b200mnist_stage_inputs(void *dst_device, const void *src_host_pinned, int64_t bytes, void *copy_stream,
+                           void *compute_stream, void *ev_slot_free, void *ev_copied) {
+    if (!dst_device || !src_host_pinned || !ev_slot_free || !ev_copied || bytes <= 0)
+        return fail_arg(1, "null pointer argument");
+    cudaStream_t cs = static_cast<cudaStream_t>(copy_stream), ms = static_cast<cudaStream_t>(compute_stream);
+    cudaError_t e = cudaStreamWaitEvent(cs, static_cast<cudaEvent_t>(ev_slot_free), 0);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dst_device, src_host_pinned, (size_t)bytes, cudaMemcpyHostToDevice, cs);
+    if (e == cudaSuccess) e = cudaEventRecord(static_cast<cudaEvent_t>(ev_copied), cs);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ms, static_cast<cudaEvent_t>(ev_copied), 0);
+    if (e != cudaSuccess) return fail_cuda(e, "stage_inputs");
+    return 0;
+}
+int b200mnist_event_record(void *event, void *stream) {
+    cudaError_t e = cudaEventRecord(static_cast<cudaEvent_t>(event), static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail_cuda(e, "cudaEventRecord");
     return 0;
 }
 

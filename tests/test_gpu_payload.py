@@ -53,7 +53,7 @@ def test_step_pipeline_matches_eager_steps():
             if pipelined:
                 loss = pipe.submit(x.pin_memory(), t.pin_memory())
                 pipe.drain()
-                assert float(loss) == float(pipe.loss_host[(pipe.steps - 1) & 1])  # D2H node delivered it
+                assert float(loss) == float(pipe.loss_host[(pipe.steps - 1) & 1])  # the kernel stored it in pinned host memory
             else:
                 loss = net.train_step(x.to(DEV), t.to(DEV), opt)
             losses.append(float(loss))
