@@ -317,6 +317,23 @@ def main():
     if not bool(torch.isfinite(pipe.loss_host).all()):
         raise SystemExit("non-finite loss in the timed region")
 
+    # ---- gradient all_reduce bus bandwidth (the second half of BASELINE.json's metric), all ranks ----
+    busbw = None
+    if world > 1:
+        buf = torch.zeros(net.flat_grads.numel(), dtype=torch.float32, device=dev)
+        for _ in range(5):
+            dist.all_reduce(buf)
+        barrier()
+        e0.record()
+        for _ in range(50):
+            dist.all_reduce(buf)
+        e1.record()
+        torch.cuda.synchronize()
+        ar_ms = max_over_ranks(e0.elapsed_time(e1) / 50)
+        nbytes_ar = buf.numel() * 4
+        busbw = {"bytes": nbytes_ar, "nccl_time_us": ar_ms * 1e3,
+                 "nccl_busbw_GBps": nbytes_ar / (ar_ms * 1e-3) * 2 * (world - 1) / world / 1e9}
+
     if rank != 0:
         if world > 1:
             net.release_graphs()  # a graph holding NCCL kernels would make destroy_process_group() block
@@ -403,6 +420,7 @@ def main():
         "kernel_us_sum": round(sum(kern_us.values()), 3),
         "ddp_exchange": (None if world == 1 else ("fused peer-memory all-reduce+SGD kernel (NVLink P2P, symmetric memory)"
                                                   if model.fused else "NCCL all_reduce + SGD kernel")),
+        "grad_allreduce": busbw,
         "cpu_baseline": cpu,
         "final_loss": loss_final,
     }

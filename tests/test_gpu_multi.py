@@ -21,3 +21,16 @@ def test_ddp_two_gpus_matches_reference_fixture(mode):
     rc = launcher.launch([os.path.join(ROOT, "tests", "ddp_worker.py"), mode], workers=1, port=port, timeout=120,
                          gpus=False if mode.startswith("fused") else None)
     assert rc == 0
+
+
+@pytest.mark.parametrize("world", [4, 8])
+@pytest.mark.parametrize("mode", ["prop-nccl", "prop-fused"])
+def test_ddp_many_gpus_properties(world, mode):
+    """BASELINE configs 3/4 at N=4 and N=8 (no reference fixture beyond ws=2): rank-ordered gradient sum, bit-identical
+    replicas, decreasing loss, smoke-dist send/recv and all_reduce bit-exactness."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    rc = launcher.launch([os.path.join(ROOT, "tests", "ddp_worker.py"), mode], workers=world - 1,
+                         port=23470 + world + (1 if mode == "prop-fused" else 0), timeout=180,
+                         gpus=False if mode == "prop-fused" else None)
+    assert rc == 0
