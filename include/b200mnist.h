@@ -181,6 +181,12 @@ int64_t b200mnist_conv1_bwd_scratch_bytes(int B);
 int b200mnist_conv1_bwd(const float *dp1, const float *p1, const uint8_t *idx1, const float *x, int B, float *gw,
                         float *gb, void *scratch, void *stream);
 
+/* Replaces the DataLoader of mnist.py:118-125 for a dataset resident on the GPU: for each of the n indices, copy
+ * image[index] (28x28 uint8, images is [n_images,784]) to data [n,1,28,28] as ((x/255) - mean)/std -- ToTensor +
+ * Normalize with the reference's fp32 roundings, bit-identical pixels -- and labels[index] to target [n]. */
+int b200mnist_gather_normalize_u8(const uint8_t *images, const int64_t *labels, const int64_t *indices, int n,
+                                  int n_images, float mean, float stdv, float *data, int64_t *target, void *stream);
+
 /* The worker's op in examples/smoke-dist/dist_sendrecv.py:32, torch.mul(inp, inp). */
 int b200mnist_square(const float *in, float *out, int64_t n, void *stream);
 

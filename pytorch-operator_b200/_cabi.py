@@ -88,6 +88,7 @@ SIGNATURES = {
     "b200mnist_conv2_bwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f, _c_f, _c_f, _c_f]),
     "b200mnist_conv1_bwd_scratch_bytes": (_i64, [_i32]),
     "b200mnist_conv1_bwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f, _c_f, _c_f]),
+    "b200mnist_gather_normalize_u8": (_i32, [_c_f, _c_f, _c_f, _i32, _i32, _f32, _f32, _c_f, _c_f, _c_f]),
     "b200mnist_square": (_i32, [_c_f, _c_f, _i64, _c_f]),
     "b200mnist_stage_inputs": (_i32, [_c_f, _c_f, _i64, _c_f, _c_f, _c_f, _c_f]),
     "b200mnist_event_record": (_i32, [_c_f, _c_f]),

@@ -384,8 +384,7 @@ int reduce_to(float *out, int n, const float *part, int nsplit, int stride, cuda
 }
 int launch_sgd(float *p, float *g, float *m, int64_t n, float lr, float mu, float scale, int first, cudaStream_t s) {
     const int blocks = (int)((n + 1023) / 1024);
-    GradSegments none{};
-    sgd_momentum_kernel<false><<<blocks, 256, 0, s>>>(p, g, m, (int)n, -lr, mu, scale, first, none);
+    sgd_momentum_kernel<<<blocks, 256, 0, s>>>(p, g, m, (int)n, -lr, mu, scale, first);
     CHECK_LAUNCH("sgd momentum", s);
     return 0;
 }
@@ -727,6 +726,21 @@ int b200mnist_conv1_bwd(const float *dp1, const float *p1, const uint8_t *idx1, 
     if (rc) return rc;
     return reduce_to(gw, 500, part, pl.c1w_split, kC1PartStride, s) ||
            reduce_to(gb, 20, part + 512, pl.c1w_split, kC1PartStride, s);
+}
+
+int b200mnist_gather_normalize_u8(const uint8_t *images, const int64_t *labels, const int64_t *indices, int n,
+                                  int n_images, float mean, float stdv, float *data, int64_t *target, void *stream) {
+    if (n == 0) return 0;
+    if (!images || !labels || !indices || !data || !target) return fail_arg(1, "null pointer argument");
+    if (n < 0 || n > 65536 || n_images < 1) return fail_arg(2, "n must be in [0, 65536] and n_images >= 1");
+    if ((reinterpret_cast<uintptr_t>(images) & 3u) || !aligned16(data))
+        return fail_arg(3, "images must be 4-byte aligned and data 16-byte aligned");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    gather_normalize_u8_kernel<<<n, 196, 0, s>>>(images, reinterpret_cast<const long long *>(labels),
+                                                reinterpret_cast<const long long *>(indices), n_images, mean, stdv, data,
+                                                reinterpret_cast<long long *>(target));
+    CHECK_LAUNCH("gather + normalize (input pipeline)", s);
+    return 0;
 }
 
 int b200mnist_square(const float *in, float *out, int64_t n, void *stream) {

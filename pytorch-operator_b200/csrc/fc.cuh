@@ -282,7 +282,6 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
 
     pdl_wait();
     __shared__ __align__(16) float w2s[kClasses * kHElems];  // 20,000 B
-    __shared__ float hs[512];
     __shared__ float wred[kHeadThreads / 32][kClasses];
     __shared__ float zs[16];
     __shared__ float dzs[16];
@@ -311,7 +310,6 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
             } else {
                 v = a.h_in[(size_t)b * kHElems + k];
             }
-            hs[k] = v;
         }
         hv[j] = v;
     }

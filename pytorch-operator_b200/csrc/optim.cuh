@@ -23,37 +23,6 @@ __device__ __forceinline__ float reduce_partials(const GradSegments &segs, int i
     return fallback;
 }
 
-// Same for four consecutive flat indices i4..i4+3 (i4 % 4 == 0) with 128-bit loads: one memory
-// round trip for up to 32 partial rows.  Elements outside every segment keep `fb`.
-__device__ __forceinline__ float4 reduce_partials4(const GradSegments &segs, int i4, float4 fb) {
-#pragma unroll
-    for (int s = 0; s < 6; ++s) {
-        if (s < segs.count) {
-            const GradSegment &sg = segs.seg[s];
-            const int r = i4 - sg.off;   // segment offsets and partial strides are multiples of 4
-            if (r >= 0 && r < sg.n) {
-                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int s0 = 0; s0 < sg.nsplit; s0 += 32) {
-                    float4 v[32];
-#pragma unroll
-                    for (int k = 0; k < 32; ++k)
-                        v[k] = (s0 + k < sg.nsplit)
-                                   ? __ldcg(reinterpret_cast<const float4 *>(sg.part + (size_t)(s0 + k) * sg.stride + r))
-                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-                    float4 a = v[0];
-#pragma unroll
-                    for (int k = 1; k < 32; ++k) { a.x += v[k].x; a.y += v[k].y; a.z += v[k].z; a.w += v[k].w; }
-                    if (s0 == 0) acc = a;
-                    else { acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w; }
-                }
-                const int left = sg.n - r;  // >= 1; elements past the segment end are bucket padding
-                return make_float4(acc.x, left > 1 ? acc.y : fb.y, left > 2 ? acc.z : fb.z, left > 3 ? acc.w : fb.w);
-            }
-        }
-    }
-    return fb;
-}
-
 // Deterministic sum of the per-row losses written by head_kernel (and of the per-row "correct"
 // flags when want_correct), by one CTA of 256 threads: strided partial sums, then a fixed tree.
 __device__ __forceinline__ void reduce_rows_block(const float *rows, int B, float scale, int want_correct,
@@ -118,22 +87,17 @@ reduce_partials_to_kernel(float *__restrict__ out, const float *__restrict__ par
     out[i] = v;
 }
 
-// One SGD+momentum step over a flat fp32 range, 4 elements per thread.  Rounding matches
-// ATen's CPU kernels bit for bit: buf*mu and +g are separate roundings (mul_ then add_),
-// p + (-lr)*buf is a single fused multiply-add (add_ with alpha).
-template <bool FUSED_FINALIZE>
+// One SGD+momentum step over a flat fp32 range, 4 elements per thread (b200mnist_sgd_momentum: the NCCL
+// DDP path and the autograd-bridge loop).  Rounding matches ATen's CPU kernels bit for bit: buf*mu and +g are
+// separate roundings (mul_ then add_), p + (-lr)*buf is a single fused multiply-add (add_ with alpha).
 __global__ void __launch_bounds__(256)
-sgd_momentum_kernel(float *__restrict__ p, float *__restrict__ g, float *__restrict__ m, int n, float neg_lr,
-                    float mu, float grad_scale, int first_step, const GradSegments segs) {
+sgd_momentum_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, int n, float neg_lr,
+                    float mu, float grad_scale, int first_step) {
     const int i4 = (blockIdx.x * 256 + threadIdx.x) * 4;
     if (i4 >= n) return;
     if (i4 + 3 < n) {
-        float4 gv = *reinterpret_cast<const float4 *>(g + i4);
-        if (FUSED_FINALIZE) {
-            gv = reduce_partials4(segs, i4, gv);
-            *reinterpret_cast<float4 *>(g + i4) = gv;  // keep the bucket inspectable (p.grad)
-        }
-        float4 pv = *reinterpret_cast<const float4 *>(p + i4);
+        const float4 gv = *reinterpret_cast<const float4 *>(g + i4);
+        const float4 pv = *reinterpret_cast<const float4 *>(p + i4);
         float4 mv = make_float4(0.f, 0.f, 0.f, 0.f);
         if (!first_step) mv = *reinterpret_cast<const float4 *>(m + i4);
         float gs[4] = {gv.x, gv.y, gv.z, gv.w}, ms[4] = {mv.x, mv.y, mv.z, mv.w}, ps[4] = {pv.x, pv.y, pv.z, pv.w};
@@ -147,9 +111,7 @@ sgd_momentum_kernel(float *__restrict__ p, float *__restrict__ g, float *__restr
         *reinterpret_cast<float4 *>(p + i4) = make_float4(ps[0], ps[1], ps[2], ps[3]);
     } else {
         for (int i = i4; i < n; ++i) {
-            float gi = g[i];
-            if (FUSED_FINALIZE) { gi = reduce_partials(segs, i, gi); g[i] = gi; }
-            gi = __fmul_rn(gi, grad_scale);
+            const float gi = __fmul_rn(g[i], grad_scale);
             const float mi = first_step ? gi : __fadd_rn(__fmul_rn(m[i], mu), gi);
             m[i] = mi;
             p[i] = __fmaf_rn(mi, neg_lr, p[i]);
@@ -222,6 +184,26 @@ __global__ void delay_kernel(unsigned long long ns) {
     do {
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     } while (t - t0 < ns);
+}
+
+// Input pipeline (mnist.py:118-125): gather a batch of 28x28 uint8 images by index and apply ToTensor +
+// Normalize -- x/255, then (x - mean)/std, each an IEEE fp32 rounding like the reference's CPU ops -- plus the
+// matching labels.  One CTA per image, 196 threads x 4 pixels (32-bit load, 128-bit store).
+__global__ void __launch_bounds__(196)
+gather_normalize_u8_kernel(const uint8_t *__restrict__ images, const long long *__restrict__ labels,
+                           const long long *__restrict__ indices, int n_images, float mean, float stdv,
+                           float *__restrict__ data, long long *__restrict__ target) {
+    const int b = blockIdx.x, t = threadIdx.x;
+    long long src = indices[b];
+    if (src < 0 || src >= n_images) src = 0;  // never read out of bounds
+    const uchar4 px = *reinterpret_cast<const uchar4 *>(images + (size_t)src * 784 + 4 * t);
+    float4 v;
+    v.x = __fdiv_rn(__fsub_rn(__fdiv_rn((float)px.x, 255.f), mean), stdv);
+    v.y = __fdiv_rn(__fsub_rn(__fdiv_rn((float)px.y, 255.f), mean), stdv);
+    v.z = __fdiv_rn(__fsub_rn(__fdiv_rn((float)px.z, 255.f), mean), stdv);
+    v.w = __fdiv_rn(__fsub_rn(__fdiv_rn((float)px.w, 255.f), mean), stdv);
+    *reinterpret_cast<float4 *>(data + (size_t)b * 784 + 4 * t) = v;
+    if (t == 0) target[b] = labels[src];
 }
 
 __global__ void __launch_bounds__(256) square_kernel(const float *__restrict__ in, float *__restrict__ out, long long n) {

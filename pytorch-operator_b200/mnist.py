@@ -6,7 +6,7 @@ Same CLI (mnist.py:78-102), same symbols (``Net``, ``train``, ``test``, ``should
 MASTER_PORT / RANK / WORLD_SIZE as injected by pkg/controller.v1/pytorch/pod.go:234-281) --
 but the training step runs on the sm_100a kernels of libb200mnist.so with one flat-bucket
 all_reduce per step.  Additive flags only: ``--synthetic N`` (seeded synthetic batches
-instead of the MNIST download, which needs a network), ``--no-graph``.
+instead of the MNIST download, which needs a network), ``--data-root``, ``--no-graph``.
 
     python -m pytorch_operator_b200.mnist --backend nccl --synthetic 200
 """
@@ -18,6 +18,7 @@ import os
 import torch
 import torch.distributed as dist
 
+from .data import DeviceMNIST, find_mnist
 from .ddp import DistributedDataParallel
 from .net import Net, StepPipeline
 from .optim import SGD
@@ -146,6 +147,8 @@ def main(argv=None):
     # additive flags
     parser.add_argument('--synthetic', type=int, default=0, metavar='NB',
                         help='train on NB seeded synthetic batches instead of downloading MNIST')
+    parser.add_argument('--data-root', default='../data', metavar='D',
+                        help="where torchvision keeps MNIST (<D>/MNIST/raw/*-ubyte[.gz]); the reference hard-codes '../data'")
     parser.add_argument('--no-graph', action='store_true', default=False,
                         help='do not capture the training step in a CUDA graph')
     args = parser.parse_args(argv)
@@ -170,6 +173,12 @@ def main(argv=None):
     if args.synthetic > 0:
         train_loader = SyntheticLoader(args.synthetic, args.batch_size, 1234 + rank)
         test_loader = SyntheticLoader(2, args.test_batch_size, 4321)
+    elif find_mnist(args.data_root, True) and find_mnist(args.data_root, False):
+        # the idx files are already on disk: keep the dataset on the GPU (no DataLoader process, no per-step H2D)
+        train_loader = DeviceMNIST.from_files(*find_mnist(args.data_root, True), batch_size=args.batch_size,
+                                              device=device, shuffle=True, seed=args.seed)
+        test_loader = DeviceMNIST.from_files(*find_mnist(args.data_root, False), batch_size=args.test_batch_size,
+                                             device=device, shuffle=False)
     else:
         from torchvision import datasets, transforms
         kwargs = {'num_workers': 1, 'pin_memory': True}

@@ -383,6 +383,16 @@ class StepPipeline:
             _cabi.check(self._lib.b200mnist_event_record(self.ev_done[k].cuda_event, main.cuda_stream), "event_record")
             self.steps += 1
             return loss
+        if host_record.is_cuda:                             # already on the device (DeviceMNIST): plain D2D on the
+            if target is None:                              # compute stream, ordered after whatever produced it
+                packed.copy_(host_record, non_blocking=True)
+            else:
+                g.x.copy_(host_record, non_blocking=True)
+                g.target.copy_(target, non_blocking=True)
+            loss = g.replay()
+            self.ev_done[k].record(main)
+            self.steps += 1
+            return loss
         self.copy_stream.wait_event(self.ev_done[k])        # slot k's previous step has consumed its inputs
         with torch.cuda.stream(self.copy_stream):           # H2D of this step's inputs, off the compute stream
             if target is None:
