@@ -200,7 +200,7 @@ int launch_conv2_fwd_tc_n(const float *in, const float *w, const float *b, float
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(conv2_fwd_tc)");
         attr_done = true;
     }
-    tc::conv2_fwd_tc_kernel<NT><<<dim3(ceil_div(B, 2), 64 / NT), tc::kThreads, tc::cv_smem_bytes<NT>(), s>>>(
+    tc::conv2_fwd_tc_kernel<NT><<<dim3(ceil_div(B, 2), 64 / NT), tc::kCvThreads, tc::cv_smem_bytes<NT>(), s>>>(
         mw, in, b, out, idx, B);
     CHECK_LAUNCH("conv2_relu_pool_fwd (tcgen05 3xTF32 implicit GEMM)", s);
     return 0;
@@ -212,8 +212,13 @@ int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *
                     : launch_conv2_fwd_tc_n<64>(in, w, b, out, idx, B, s);
 }
 // The tensor-core conv2 forward is correct (tests/test_gpu_tc.py) but, in round 1, slower than the FFMA2 direct
-// convolution at every batch size (28.6 vs 14.1 us at B=64, 347 vs 242 us at B=4096: the weight-tile TMA is issued
-// only when its stage frees up, so its latency is exposed every k-block), so it is opt-in: B200MNIST_CONV2_TC=1.
+// convolution at every batch size (23.9 vs 14.1 us at B=64, 283 vs 242 us at B=4096), so it is opt-in:
+// B200MNIST_CONV2_TC=1.  Why: with N = 50 output channels the 3xTF32 product is shared-memory-bandwidth bound --
+// every K=8 MMA re-reads 4 KB of A and 2 KB of B from shared memory (48 cycles at 128 B/clk against 32 cycles of
+// math), three times per k-slice for the hi/lo combinations, on top of the builders' own 50 KB of tile traffic per
+// k-block -- so the tensor pipe cannot get past ~25 % (ncu: 17-27 % on the fc1 GEMMs, which have the same shape).
+// The fix is an A operand resident in TMEM (tcgen05.cp once, then TS-mode MMAs) and a persistent CTA that amortises
+// the prologue; left for the next round.
 int g_conv2_tc = -1;
 bool conv2_tc_enabled() {
     if (g_conv2_tc < 0) {

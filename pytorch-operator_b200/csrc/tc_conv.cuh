@@ -6,7 +6,7 @@
 // staged in shared memory (a 512-entry offset table turns k into ic*144 + ky*12 + kx), split each value into
 // hi/lo and write both K-major 128B-swizzled tiles in place -- the swizzle makes the 16-byte stores of the eight
 // lanes of a phase bank-conflict free.  The weight tile arrives by TMA (out-of-range rows/columns are zero filled)
-// and is split by the same warps.  Rows are ordered (image, pool window, window slot), so the 2x2 max-pool and its
+// through a 6-deep ring that runs ahead of the A stages and is split by the same warps.  Rows are ordered (image, pool window, window slot), so the 2x2 max-pool and its
 // arg-max are three warp shuffles per channel in the epilogue, and only the pooled 4x4 map is written.
 #pragma once
 #include "tc_gemm.cuh"
@@ -14,13 +14,18 @@
 namespace b200mnist {
 namespace tc {
 
-constexpr int kCvStages = 3;
+constexpr int kCvStages = 3;                 // A_hi/A_lo/B_hi/B_lo stages consumed by the MMA
+constexpr int kCvRing = 6;                   // raw weight tiles in flight (TMA runs this far ahead of the builders)
+constexpr int kCvBuilders = 256;             // 8 builder warps: two threads per GEMM row
+constexpr int kCvThreads = 64 + kCvBuilders;
 constexpr int kCvImgBytes = 2 * kP1Elems * 4;                      // 23,040 B: two staged images
 template <int NT> __host__ __device__ constexpr int cv_stage_bytes() { return 2 * kTileA + 2 * NT * kBK * 4; }
-template <int NT> __host__ __device__ constexpr int cv_smem_bytes() { return kCvStages * cv_stage_bytes<NT>() + kCvImgBytes + 2048 /*table*/ + 1024 + 256; }
+template <int NT> __host__ __device__ constexpr int cv_smem_bytes() {
+    return kCvStages * cv_stage_bytes<NT>() + kCvRing * NT * kBK * 4 + kCvImgBytes + 2048 /*table*/ + 1024 + 256;
+}
 
 template <int NT>  // N tile: 64 (all 50 channels in one CTA) or 32 (two CTAs per image pair: small batches)
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kCvThreads, 1)
 conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__restrict__ in,
                     const float *__restrict__ bias, float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
     constexpr int kTileBn = NT * kBK * 4;
@@ -28,18 +33,23 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
     constexpr int kNkb = 16;  // K = 500 padded to 512
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    float *img_s = reinterpret_cast<float *>(smem + kCvStages * kStage);                 // [2][20][144]
-    int *koff = reinterpret_cast<int *>(smem + kCvStages * kStage + kCvImgBytes);        // [512]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kCvStages * kStage + kCvImgBytes + 2048);
-    uint64_t *b_full = bars, *built = bars + kCvStages, *empty = bars + 2 * kCvStages, *acc_full = bars + 3 * kCvStages;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 3 * kCvStages + 1);
+    uint8_t *ring = smem + kCvStages * kStage;                                            // [kCvRing][NT x 32 fp32] raw W tiles
+    float *img_s = reinterpret_cast<float *>(ring + kCvRing * kTileBn);                   // [2][20][144]
+    int *koff = reinterpret_cast<int *>(reinterpret_cast<uint8_t *>(img_s) + kCvImgBytes);  // [512]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(koff) + 2048);
+    uint64_t *w_full = bars, *w_empty = bars + kCvRing, *built = bars + 2 * kCvRing, *empty = built + kCvStages;
+    uint64_t *acc_full = empty + kCvStages;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b0 = blockIdx.x * 2, n0 = blockIdx.y * NT;
 
     if (threadIdx.x == 0) {
+        for (int r = 0; r < kCvRing; ++r) {
+            mbar_init(smem_u32(&w_full[r]), 1);
+            mbar_init(smem_u32(&w_empty[r]), kCvBuilders);
+        }
         for (int s = 0; s < kCvStages; ++s) {
-            mbar_init(smem_u32(&b_full[s]), 1);
-            mbar_init(smem_u32(&built[s]), 128);
+            mbar_init(smem_u32(&built[s]), kCvBuilders);
             mbar_init(smem_u32(&empty[s]), 1);
         }
         mbar_init(smem_u32(acc_full), 1);
@@ -47,17 +57,17 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(NT < 32 ? 32 : NT)
+                     "r"(NT)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (warp >= 2) {
-        // stage the two images and the k -> offset table (builder warps only need them, but everybody syncs below)
+        // stage the two images and the k -> offset table
         const int t = threadIdx.x - 64;
-        float4 iv[12];
+        float4 iv[6];
 #pragma unroll
-        for (int j = 0; j < 12; ++j) {
-            const int i = t + j * 128;
+        for (int j = 0; j < 6; ++j) {
+            const int i = t + j * kCvBuilders;
             iv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (i < 2 * kP1Elems / 4) {
                 const int img = i / (kP1Elems / 4), b = b0 + img;
@@ -65,11 +75,11 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
             }
         }
 #pragma unroll
-        for (int j = 0; j < 12; ++j) {
-            const int i = t + j * 128;
+        for (int j = 0; j < 6; ++j) {
+            const int i = t + j * kCvBuilders;
             if (i < 2 * kP1Elems / 4) reinterpret_cast<float4 *>(img_s)[i] = iv[j];
         }
-        for (int k = t; k < 512; k += 128) {
+        for (int k = t; k < 512; k += kCvBuilders) {
             const int ic = k / 25, r = k - ic * 25, ky = r / 5, kx = r - ky * 5;
             koff[k] = k < 500 ? ic * 144 + ky * 12 + kx : -1;
         }
@@ -80,14 +90,14 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
     const uint32_t tmem_d = *tmem_slot;
 
     if (warp == 0) {
-        // ===== TMA producer: weight tiles =====
+        // ===== TMA producer: raw weight tiles, kCvRing deep (independent of the A stages) =====
         if (lane == 0) {
             for (int kb = 0; kb < kNkb; ++kb) {
-                const int s = kb % kCvStages, ph = (kb / kCvStages) & 1;
-                mbar_wait(smem_u32(&empty[s]), ph ^ 1);
-                const uint32_t bar = smem_u32(&b_full[s]);
+                const int r = kb % kCvRing, ph = (kb / kCvRing) & 1;
+                mbar_wait(smem_u32(&w_empty[r]), ph ^ 1);
+                const uint32_t bar = smem_u32(&w_full[r]);
                 mbar_arrive_expect_tx(bar, kTileBn);
-                tma_load_2d(smem_u32(smem + s * kStage + 2 * kTileA), &map_w, kb * kBK, n0, bar);
+                tma_load_2d(smem_u32(ring + r * kTileBn), &map_w, kb * kBK, n0, bar);
             }
         }
     } else if (warp == 1) {
@@ -114,8 +124,9 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
             umma_commit(smem_u32(acc_full));
         }
     } else {
-        // ===== builders (warps 2-5): im2col rows -> A_hi / A_lo, split the weight tile; then epilogue =====
-        const int t = threadIdx.x - 64;               // GEMM row of this thread
+        // ===== builders (warps 2-9): im2col rows -> A_hi / A_lo, split the weight tile; then epilogue =====
+        const int bt = threadIdx.x - 64;
+        const int t = bt & 127, half = bt >> 7;       // GEMM row, and which 4 of the row's 8 16-byte units
         const int img = t >> 6, win = (t >> 2) & 15, q = t & 3;
         const int oy = 2 * (win >> 2) + (q >> 1), ox = 2 * (win & 3) + (q & 1);
         const float *src = img_s + img * kP1Elems + oy * 12 + ox;
@@ -125,7 +136,8 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
             mbar_wait(smem_u32(&empty[s]), ph ^ 1);   // the MMAs that read this stage last time have completed
             uint8_t *st = smem + s * kStage;
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
+            for (int jj = 0; jj < 4; ++jj) {
+                const int j4 = half * 4 + jj;
                 const int4 ko = *reinterpret_cast<const int4 *>(koff + kb * kBK + j4 * 4);
                 const float v0 = ko.x >= 0 ? src[ko.x] : 0.f, v1 = ko.y >= 0 ? src[ko.y] : 0.f;
                 const float v2 = ko.z >= 0 ? src[ko.z] : 0.f, v3 = ko.w >= 0 ? src[ko.w] : 0.f;
@@ -138,30 +150,35 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
                 *reinterpret_cast<uint4 *>(st + o) = hi;
                 *reinterpret_cast<uint4 *>(st + kTileA + o) = lo;
             }
-            mbar_wait(smem_u32(&b_full[s]), ph);      // weight tile has landed: split it in place
+            // weight tile: raw (TMA ring) -> hi / lo in this stage, same offsets (the swizzled layout is preserved)
+            const int r = kb % kCvRing, rph = (kb / kCvRing) & 1;
+            mbar_wait(smem_u32(&w_full[r]), rph);
+            const uint4 *braw = reinterpret_cast<const uint4 *>(ring + r * kTileBn);
             uint4 *bh = reinterpret_cast<uint4 *>(st + 2 * kTileA), *bl = reinterpret_cast<uint4 *>(st + 2 * kTileA + kTileBn);
 #pragma unroll
-            for (int j = 0; j < kTileBn / 16 / 128; ++j) {
-                const uint4 v = bh[t + j * 128];
+            for (int j = 0; j < kTileBn / 16 / kCvBuilders; ++j) {
+                const uint4 v = braw[bt + j * kCvBuilders];
                 uint4 hi = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u), lo;
                 lo.x = __float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x));
                 lo.y = __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y));
                 lo.z = __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z));
                 lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
-                bh[t + j * 128] = hi;
-                bl[t + j * 128] = lo;
+                bh[bt + j * kCvBuilders] = hi;
+                bl[bt + j * kCvBuilders] = lo;
             }
+            mbar_arrive(smem_u32(&w_empty[r]));       // ring slot may be refilled
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(smem_u32(&built[s]));
         }
         // ---- epilogue: bias, 2x2 max-pool with arg-max (4 consecutive rows = one window), ReLU ----
-        mbar_wait(smem_u32(acc_full), 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int qt = warp & 3;                      // TMEM lane quarter of this warp
-        const int row = qt * 32 + lane;               // == t's row in this quarter's numbering
-        const int e_img = row >> 6, e_win = (row >> 2) & 15, b = b0 + e_img;
-#pragma unroll
-        for (int c = 0; c < NT / 32; ++c) {
+        // warp w owns TMEM lane quarter w % 4; the two warps of a quarter take 32 columns each
+        const int c = (warp - 2) >> 2;
+        if (c * 32 < NT) {
+            mbar_wait(smem_u32(acc_full), 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int qt = warp & 3;
+            const int row = qt * 32 + lane;
+            const int e_img = row >> 6, e_win = (row >> 2) & 15, b = b0 + e_img;
             uint32_t r[32];
             tmem_ld32(tmem_d + ((uint32_t)(qt * 32) << 16) + c * 32, r);
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -189,7 +206,7 @@ conv2_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_w, const float *__re
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(NT < 32 ? 32 : NT) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(NT) : "memory");
     }
 }
 
