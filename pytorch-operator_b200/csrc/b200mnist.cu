@@ -81,6 +81,18 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
         note_launch(where, stream);                           \
     } while (0)
 
+// Opt a kernel in to more than 48 KB of dynamic shared memory, once per device (function attributes are per device).
+template <typename K>
+cudaError_t ensure_dynamic_smem(K kernel, int bytes, unsigned long long *done_mask) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64 && (*done_mask >> dev) & 1ull) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess && dev >= 0 && dev < 64) *done_mask |= 1ull << dev;
+    return e;
+}
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -193,13 +205,9 @@ int launch_conv2_fwd_tc_n(const float *in, const float *w, const float *b, float
                           cudaStream_t s) {
     CUtensorMap mw;
     if (!tc::make_map_kmajor(&mw, w, 50, 500, 500, NT)) return fail_arg(8, kTmapErr);
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(tc::conv2_fwd_tc_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             tc::cv_smem_bytes<NT>());
-        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(conv2_fwd_tc)");
-        attr_done = true;
-    }
+    static unsigned long long attr_mask = 0;
+    cudaError_t ea = ensure_dynamic_smem(tc::conv2_fwd_tc_kernel<NT>, tc::cv_smem_bytes<NT>(), &attr_mask);
+    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_fwd_tc)");
     tc::conv2_fwd_tc_kernel<NT><<<dim3(ceil_div(B, 2), 64 / NT), tc::kCvThreads, tc::cv_smem_bytes<NT>(), s>>>(
         mw, in, b, out, idx, B);
     CHECK_LAUNCH("conv2_relu_pool_fwd (tcgen05 3xTF32 implicit GEMM)", s);
@@ -245,13 +253,9 @@ int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float
 constexpr int kTcMinBatch = 1024;
 template <bool A_MN, bool B_MN, int EPI>
 int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, const tc::TcGemmArgs &a, const char *what, cudaStream_t s) {
-    static bool attr_done = false;  // one per template instantiation
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(tc::gemm_tc_kernel<A_MN, B_MN, EPI>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBytes);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(gemm_tc)");
-        attr_done = true;
-    }
+    static unsigned long long attr_mask = 0;  // one per template instantiation
+    cudaError_t ea = ensure_dynamic_smem(tc::gemm_tc_kernel<A_MN, B_MN, EPI>, tc::kSmemBytes, &attr_mask);
+    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(gemm_tc)");
     const int ncols = a.N + (EPI == tc::kEpiWgrad ? 1 : 0);  // wgrad carries one extra column (the bias gradient)
     tc::gemm_tc_kernel<A_MN, B_MN, EPI><<<dim3(ceil_div(ncols, tc::kBN), ceil_div(a.M, tc::kBM)), tc::kThreads,
                                          tc::kSmemBytes, s>>>(ma, mb, a);
@@ -337,13 +341,9 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
 int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const float *p2, const uint8_t *i2,
                      const float *p1, const float *w, int B, float *dp1, float *c2w_part, const Plan &pl,
                      cudaStream_t s) {
-    static bool attr_done = false;  // per process; setting it again is harmless
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(conv2_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             kConv2BwdSmemBytes);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(conv2_bwd)");
-        attr_done = true;
-    }
+    static unsigned long long attr_mask = 0;
+    cudaError_t ea = ensure_dynamic_smem(conv2_bwd_kernel, kConv2BwdSmemBytes, &attr_mask);
+    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_bwd)");
     Conv2BwdArgs a{};
     a.dp2 = dp2; a.p2 = p2; a.p1 = p1; a.w = w; a.i2 = i2; a.dp1 = dp1; a.part = c2w_part;
     a.split_stride = split_stride; a.nsplit = nsplit; a.B = B;

@@ -21,6 +21,15 @@ constexpr int kXElems = 784, kP1Elems = 2880, kP2Elems = 800, kHElems = 500, kCl
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Wall-clock bound for device-side waits (mbarrier polls, cross-GPU flags): a wait that has not been satisfied
+// after kSpinTimeoutNs traps -- the launch fails with an error instead of hanging the GPU.
+constexpr unsigned long long kSpinTimeoutNs = 10ull * 1000 * 1000 * 1000;
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -14,7 +14,7 @@
 // The exchange is one-shot (each rank reads (ws-1) x 1.7 MB): at this message size the all-reduce is latency
 // bound, and a one-shot read has a single barrier + a single NVLink round trip on the critical path.
 // Flags carry a monotonically increasing epoch kept in device memory, so the kernel is CUDA-graph replayable
-// with constant arguments.  All spins are bounded (trap instead of hanging the GPU).
+// with constant arguments.  All spins are bounded by wall-clock time (10 s, then trap instead of hanging the GPU).
 #pragma once
 #include "common.cuh"
 
@@ -38,10 +38,15 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
 }
 // wait until *p has reached `want` (epochs only grow; signed difference is wrap-safe)
 __device__ __forceinline__ void spin_until(const unsigned *p, unsigned want) {
-    for (unsigned spin = 0; spin < (1u << 27); ++spin) {
+    unsigned long long t0 = 0;
+    for (unsigned spin = 0;; ++spin) {
         if ((int)(ld_acquire_sys(p) - want) >= 0) return;
+        if ((spin & 1023u) == 1023u) {   // a peer that never arrives (crashed rank) must not hang this GPU
+            const unsigned long long now = global_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > kSpinTimeoutNs) __trap();
+        }
     }
-    __trap();
 }
 
 // signal pad layout (u32): [0..7] "gradient ready" flags by source rank, [8..15] "done reading" flags.

@@ -49,9 +49,10 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// Bounded wait: ~2 s worth of polling, then trap (a lost barrier must not hang the box).
+// Bounded wait: poll, and trap after 10 s of wall-clock time (a lost barrier must not hang the box).
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+    unsigned long long t0 = 0;
+    for (uint32_t spin = 0;; ++spin) {
         uint32_t ok;
         asm volatile("{\n\t.reg .pred p;\n\t"
                      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -60,8 +61,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
                      : "r"(bar), "r"(parity)
                      : "memory");
         if (ok) return;
+        if ((spin & 1023u) == 1023u) {
+            const unsigned long long now = global_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > kSpinTimeoutNs) __trap();
+        }
     }
-    __trap();
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
