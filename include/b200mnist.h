@@ -122,12 +122,14 @@ int b200mnist_conv1_relu_pool_fwd(const float *x, const float *w, const float *b
  * out [B,50,4,4] (= the [B,800] view of mnist.py:30). */
 int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
                                   int B, void *stream);
-/* The same conv2 + ReLU + max-pool (mnist.py:28-29) as an implicit GEMM on the tensor cores: im2col rows built in
- * shared memory, weight tiles by TMA, tcgen05.mma kind::tf32 with the 3xTF32 split, pooling in the epilogue.
- * Experimental in round 1 (slower than the direct convolution; the fused step uses it only with
- * B200MNIST_CONV2_TC=1 in the environment). */
+/* The same conv2 + ReLU + max-pool (mnist.py:28-29) on the tensor cores: a shifted-window implicit GEMM (the image
+ * pair is staged once in shared memory; each of the 25 kernel offsets is an MMA whose operand descriptor points at
+ * the same planes shifted by (ky,kx)), tcgen05.mma kind::tf32 with the 3xTF32 split, pooling in the epilogue.
+ * `scratch` (b200mnist_conv2_fwd_tc_scratch_bytes() bytes, 16-byte aligned) receives the hi/lo-split weights.
+ * The fused step uses this path when B200MNIST_CONV2_TC=1 is set in the environment. */
+int64_t b200mnist_conv2_fwd_tc_scratch_bytes(void);
 int b200mnist_conv2_relu_pool_fwd_tc(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
-                                     int B, void *stream);
+                                     int B, void *scratch, void *stream);
 /* F.relu(fc1(x)), mnist.py:31.  in [B,800], w [500,800], out [B,500].  `scratch` must hold
  * b200mnist_fc1_scratch_bytes(B) bytes (split-K partial sums). */
 int64_t b200mnist_fc1_scratch_bytes(int B);

@@ -75,7 +75,8 @@ SIGNATURES = {
     "b200mnist_forward_backward_phase": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv1_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv2_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
-    "b200mnist_conv2_relu_pool_fwd_tc": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
+    "b200mnist_conv2_fwd_tc_scratch_bytes": (_i64, []),
+    "b200mnist_conv2_relu_pool_fwd_tc": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f]),
     "b200mnist_fc1_scratch_bytes": (_i64, [_i32]),
     "b200mnist_fc1_relu_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f]),
     "b200mnist_fc1_relu_fwd_tc": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f]),

@@ -14,7 +14,7 @@
 #include "optim.cuh"
 #include "peer_allreduce.cuh"
 #include "tc_gemm.cuh"
-#include "tc_conv.cuh"
+#include "tc_conv_bwd.cuh"
 
 using namespace b200mnist;
 
@@ -103,10 +103,12 @@ struct Plan {
     int fc1_split, fc1_kchunk;  // fc1 forward split-K
     int dg_split, dg_kchunk;    // fc1 data-gradient split-K
     int fc2w_split, fc2w_rows;  // fc2 weight-gradient batch split
-    int c2w_split;              // conv2 weight-gradient batch split
+    int c2w_split;              // conv2 weight-gradient batch split (= number of partials)
+    bool c2w_tc, c2dg_tc;       // conv2 weight / data gradient on the tensor cores (tc_conv_bwd.cuh)
     int c1w_split;              // conv1 weight-gradient batch split
     int c2dg_gx;                // conv2 data-gradient CTAs per channel tile
 };
+bool tc_path_enabled(const char *env, int B);
 Plan make_plan(int B) {
     Plan p;
     const int gy = ceil_div(B, 64);
@@ -139,6 +141,10 @@ Plan make_plan(int B) {
     }
     if (ov[2] > 0) p.c2w_split = clampi(ov[2], 1, 32);
     if (ov[3] > 0) p.c2dg_gx = clampi(ov[3], 1, B);
+    // conv2 backward on the tensor cores: auto from kTcMinBatch up; B200MNIST_CONV2_WGRAD_TC / _DGRAD_TC = 1 / 0 force
+    p.c2w_tc = tc_path_enabled("B200MNIST_CONV2_WGRAD_TC", B);
+    p.c2dg_tc = tc_path_enabled("B200MNIST_CONV2_DGRAD_TC", B);
+    if (p.c2w_tc) p.c2w_split = B < tc::kWgMaxSlices ? B : tc::kWgMaxSlices;
     return p;
 }
 
@@ -149,6 +155,8 @@ struct Workspace {
     float *p1, *p2, *h, *logp, *dz2, *dz1, *dp1, *rows;
     uint8_t *i1, *i2;
     float *fc1_part, *dp2_part, *fc2w_part, *c2w_part, *c1w_part;
+    float *w2s;  // conv2.weight split into hi/lo tensor-core operands (tc_conv.cuh)
+    float *wd;   // the same for the data-gradient GEMM (tc_conv_bwd.cuh)
     size_t bytes;
 };
 Workspace carve(void *base, int B) {
@@ -178,6 +186,8 @@ Workspace carve(void *base, int B) {
     w.fc2w_part = static_cast<float *>(take((size_t)32 * kFc2PartStride * 4));
     w.c2w_part = static_cast<float *>(take((size_t)32 * kC2PartStride * 4));
     w.c1w_part = static_cast<float *>(take((size_t)kMaxGradSplit * kC1PartStride * 4));
+    w.w2s = static_cast<float *>(take((size_t)tc::kWnScratchFloats * 4));
+    w.wd = static_cast<float *>(take((size_t)tc::kDgScratchFloats * 4));
     w.bytes = off;
     return w;
 }
@@ -199,47 +209,36 @@ int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out,
     return 0;
 }
 const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)";
-// conv2 forward as an implicit GEMM on the tensor cores (tcgen05 3xTF32, im2col built in shared memory)
-template <int NT>
-int launch_conv2_fwd_tc_n(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
-                          cudaStream_t s) {
-    CUtensorMap mw;
-    if (!tc::make_map_kmajor(&mw, w, 50, 500, 500, NT)) return fail_arg(8, kTmapErr);
+// conv2 forward on the tensor cores (tcgen05 3xTF32, shifted-window implicit GEMM; tc_conv.cuh).  `w2s` receives the
+// hi/lo-split, operand-ordered copy of conv2.weight (tc::kWnScratchFloats floats), rebuilt on every call.
+int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B, float *w2s,
+                        cudaStream_t s) {
+    constexpr int NT = 32;
     static unsigned long long attr_mask = 0;
-    cudaError_t ea = ensure_dynamic_smem(tc::conv2_fwd_tc_kernel<NT>, tc::cv_smem_bytes<NT>(), &attr_mask);
-    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_fwd_tc)");
-    tc::conv2_fwd_tc_kernel<NT><<<dim3(ceil_div(B, 2), 64 / NT), tc::kCvThreads, tc::cv_smem_bytes<NT>(), s>>>(
-        mw, in, b, out, idx, B);
-    CHECK_LAUNCH("conv2_relu_pool_fwd (tcgen05 3xTF32 implicit GEMM)", s);
+    cudaError_t ea = ensure_dynamic_smem(tc::conv2_fwd_win_kernel<NT>, tc::wn_smem_bytes<NT>(), &attr_mask);
+    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_fwd_win)");
+    CHECK_PDL(launch_pdl(tc::conv2_weight_split_kernel<NT>, dim3(25), dim3(256), 0, s, w, w2s), "conv2 weight split (hi/lo)", s);
+    const int npairs = (B + 1) / 2;
+    CHECK_PDL(launch_pdl(tc::conv2_fwd_win_kernel<NT>, dim3(npairs < 74 ? npairs : 74, 64 / NT), dim3(tc::kWnThreads),
+                         (size_t)tc::wn_smem_bytes<NT>(), s, in, (const float *)w2s, b, out, idx, B),
+              "conv2_relu_pool_fwd (tcgen05 3xTF32 shifted-window GEMM)", s);
     return 0;
 }
-int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
-                        cudaStream_t s) {
-    // small batches: two CTAs (32 channels each) per image pair so that more SMs take part
-    return B <= 296 ? launch_conv2_fwd_tc_n<32>(in, w, b, out, idx, B, s)
-                    : launch_conv2_fwd_tc_n<64>(in, w, b, out, idx, B, s);
+// Which conv2 forward runs inside the fused step: the tensor-core kernel wins from a few hundred images up (B=4096:
+// 141 vs 228 us; B=1024: 44 vs 61 us) and loses at the reference batch (B=64: its 64 CTAs pay the 128 KB weight load
+// and a 150-MMA chain each, 11 vs 9 us), so it switches on together with the tcgen05 fc1 GEMMs at kTcMinBatch.
+// B200MNIST_CONV2_TC=1 / =0 forces it on / off (tests, profiling).
+constexpr int kTcMinBatch = 1024;
+bool tc_path_enabled(const char *env, int B) {   // read at every (uncaptured) launch: a few hundred ns, lets tests toggle it
+    const char *e = getenv(env);
+    return (!e || !e[0]) ? B >= kTcMinBatch : e[0] == '1';
 }
-// The tensor-core conv2 forward is correct (tests/test_gpu_tc.py) but, in round 1, slower than the FFMA2 direct
-// convolution at every batch size (23.9 vs 14.1 us at B=64, 283 vs 242 us at B=4096), so it is opt-in:
-// B200MNIST_CONV2_TC=1.  Why: with N = 50 output channels the 3xTF32 product is shared-memory-bandwidth bound --
-// every K=8 MMA re-reads 4 KB of A and 2 KB of B from shared memory (48 cycles at 128 B/clk against 32 cycles of
-// math), three times per k-slice for the hi/lo combinations, on top of the builders' own 50 KB of tile traffic per
-// k-block -- so the tensor pipe cannot get past ~25 % (ncu: 17-27 % on the fc1 GEMMs, which have the same shape).
-// The fix is an A operand resident in TMEM (tcgen05.cp once, then TS-mode MMAs) and a persistent CTA that amortises
-// the prologue; left for the next round.
-int g_conv2_tc = -1;
-bool conv2_tc_enabled() {
-    if (g_conv2_tc < 0) {
-        const char *e = getenv("B200MNIST_CONV2_TC");
-        g_conv2_tc = (e && e[0] == '1') ? 1 : 0;
-    }
-    return g_conv2_tc != 0;
-}
+bool conv2_tc_enabled(int B) { return tc_path_enabled("B200MNIST_CONV2_TC", B); }
 int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
                           cudaStream_t s);
-int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
+int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B, float *w2s,
                      cudaStream_t s) {
-    if (conv2_tc_enabled()) return launch_conv2_fwd_tc(in, w, b, out, idx, B, s);
+    if (w2s && conv2_tc_enabled(B)) return launch_conv2_fwd_tc(in, w, b, out, idx, B, w2s, s);
     return launch_conv2_fwd_simt(in, w, b, out, idx, B, s);
 }
 int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
@@ -249,8 +248,7 @@ int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float
               "conv2_relu_pool_fwd", s);
     return 0;
 }
-// fc1 forward on the tensor cores (tcgen05 3xTF32, TMA-fed): large batches only.
-constexpr int kTcMinBatch = 1024;
+// fc1 forward on the tensor cores (tcgen05 3xTF32, TMA-fed): large batches only (kTcMinBatch).
 template <bool A_MN, bool B_MN, int EPI>
 int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, const tc::TcGemmArgs &a, const char *what, cudaStream_t s) {
     static unsigned long long attr_mask = 0;  // one per template instantiation
@@ -339,7 +337,7 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
     return 0;
 }
 int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const float *p2, const uint8_t *i2,
-                     const float *p1, const float *w, int B, float *dp1, float *c2w_part, const Plan &pl,
+                     const float *p1, const float *w, int B, float *dp1, float *c2w_part, float *wd, const Plan &pl,
                      cudaStream_t s) {
     static unsigned long long attr_mask = 0;
     cudaError_t ea = ensure_dynamic_smem(conv2_bwd_kernel, kConv2BwdSmemBytes, &attr_mask);
@@ -348,8 +346,42 @@ int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const fl
     a.dp2 = dp2; a.p2 = p2; a.p1 = p1; a.w = w; a.i2 = i2; a.dp1 = dp1; a.part = c2w_part;
     a.split_stride = split_stride; a.nsplit = nsplit; a.B = B;
     a.wg_gy = pl.c2w_split; a.n_wg = 5 * pl.c2w_split; a.dg_gx = pl.c2dg_gx;
-    CHECK_PDL(launch_pdl(conv2_bwd_kernel, dim3(a.n_wg + 5 * a.dg_gx), dim3(kConvBwdThreads), kConv2BwdSmemBytes, s, a),
-              "conv2 backward (wgrad + dgrad)", s);
+    const bool dg_tc = pl.c2dg_tc && wd != nullptr;
+    if (!dg_tc && !pl.c2w_tc) {
+        CHECK_PDL(launch_pdl(conv2_bwd_kernel, dim3(a.n_wg + 5 * a.dg_gx), dim3(kConvBwdThreads), kConv2BwdSmemBytes, s, a),
+                  "conv2 backward (wgrad + dgrad)", s);
+        return 0;
+    }
+    if (dg_tc) {
+        static unsigned long long tc_mask = 0;
+        ea = ensure_dynamic_smem(tc::conv2_dgrad_tc_kernel, tc::kDgSmemBytes, &tc_mask);
+        if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_dgrad_tc)");
+        CHECK_PDL(launch_pdl(tc::conv2_dgrad_weight_split_kernel, dim3(4 * tc::kDgChunks), dim3(128), 0, s, w, wd),
+                  "conv2 dgrad weight split (hi/lo)", s);
+        tc::Conv2DgradTcArgs t{};
+        t.dp2 = dp2; t.p2 = p2; t.wd = wd; t.i2 = i2; t.dp1 = dp1; t.split_stride = split_stride; t.nsplit = nsplit; t.B = B;
+        const int npairs = (B + 1) / 2;
+        CHECK_PDL(launch_pdl(tc::conv2_dgrad_tc_kernel, dim3(npairs < 37 ? npairs : 37, 4), dim3(tc::kDgThreads),
+                             (size_t)tc::kDgSmemBytes, s, t),
+                  "conv2 dgrad (tcgen05 3xTF32 GEMM + col2im)", s);
+    }
+    if (pl.c2w_tc) {
+        static unsigned long long tc_mask = 0;
+        ea = ensure_dynamic_smem(tc::conv2_wgrad_tc_kernel, tc::kWgSmemBytes, &tc_mask);
+        if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_wgrad_tc)");
+        tc::Conv2WgradTcArgs t{};
+        t.dp2 = dp2; t.p2 = p2; t.p1 = p1; t.i2 = i2; t.part = c2w_part; t.split_stride = split_stride; t.nsplit = nsplit;
+        t.B = B; t.nslices = pl.c2w_split;
+        CHECK_PDL(launch_pdl(tc::conv2_wgrad_tc_kernel, dim3(pl.c2w_split, 5), dim3(tc::kWgThreads), (size_t)tc::kWgSmemBytes,
+                             s, t),
+                  "conv2 wgrad (tcgen05 3xTF32, all four hi/lo products per MMA)", s);
+    }
+    if (!dg_tc || !pl.c2w_tc) {   // the remaining half on the fp32 SIMT kernel
+        if (dg_tc) a.dg_gx = 0;
+        if (pl.c2w_tc) a.n_wg = 0;
+        CHECK_PDL(launch_pdl(conv2_bwd_kernel, dim3(a.n_wg + 5 * a.dg_gx), dim3(kConvBwdThreads), kConv2BwdSmemBytes, s, a),
+                  dg_tc ? "conv2 wgrad" : "conv2 dgrad", s);
+    }
     return 0;
 }
 int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
@@ -409,12 +441,12 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     int rc;
     if (phase == 2) {
         if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B,
-                                   w.dp1, w.c2w_part, pl, s)))
+                                   w.dp1, w.c2w_part, w.wd, pl, s)))
             return rc;
         return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
     }
     if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s))) return rc;
-    if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, s))) return rc;
+    if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, w.w2s, s))) return rc;
     int nsplit = 0;
     if ((rc = launch_fc1_fwd(w.p2, P + kOffF1W, P + kOffF1B, w.h, w.fc1_part, B, pl, s, &nsplit))) return rc;
     HeadArgs a{};
@@ -432,7 +464,7 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
         return rc;
     if (phase == 1) return 0;
     if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B, w.dp1,
-                               w.c2w_part, pl, s)))
+                               w.c2w_part, w.wd, pl, s)))
         return rc;
     return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
 }
@@ -570,15 +602,17 @@ int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *
     if (!in || !w || !bias || !out || !idx) return fail_arg(1, "null pointer argument");
     if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
     if (!aligned16(in)) return fail_arg(3, "in must be 16-byte aligned");
-    return launch_conv2_fwd(in, w, bias, out, idx, B, static_cast<cudaStream_t>(stream));
+    return launch_conv2_fwd(in, w, bias, out, idx, B, nullptr, static_cast<cudaStream_t>(stream));
 }
 
+int64_t b200mnist_conv2_fwd_tc_scratch_bytes(void) { return (int64_t)tc::kWnScratchFloats * 4; }
+
 int b200mnist_conv2_relu_pool_fwd_tc(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
-                                     int B, void *stream) {
-    if (!in || !w || !bias || !out || !idx) return fail_arg(1, "null pointer argument");
+                                     int B, void *scratch, void *stream) {
+    if (!in || !w || !bias || !out || !idx || !scratch) return fail_arg(1, "null pointer argument");
     if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
-    if (!aligned16(in) || !aligned16(w)) return fail_arg(3, "in/w must be 16-byte aligned");
-    return launch_conv2_fwd_tc(in, w, bias, out, idx, B, static_cast<cudaStream_t>(stream));
+    if (!aligned16(in) || !aligned16(scratch)) return fail_arg(3, "in/scratch must be 16-byte aligned");
+    return launch_conv2_fwd_tc(in, w, bias, out, idx, B, static_cast<float *>(scratch), static_cast<cudaStream_t>(stream));
 }
 
 int64_t b200mnist_fc1_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)10 * B * 512 * 4; }
@@ -701,7 +735,9 @@ int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const f
     return reduce_to(gb2, 10, fc2w_part + 5056, pl.fc2w_split, kFc2PartStride, s);
 }
 
-int64_t b200mnist_conv2_bwd_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)32 * kC2PartStride * 4; }
+int64_t b200mnist_conv2_bwd_scratch_bytes(int B) {
+    return B < 1 ? -1 : (int64_t)32 * kC2PartStride * 4 + (int64_t)tc::kDgScratchFloats * 4;
+}
 
 int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, const float *p1, const float *w, int B,
                         float *gw, float *gb, float *dp1, void *scratch, void *stream) {
@@ -711,7 +747,7 @@ int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, 
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const Plan pl = make_plan(B);
     float *part = static_cast<float *>(scratch);
-    int rc = launch_conv2_bwd(dp2, 1, 0, p2, idx2, p1, w, B, dp1, part, pl, s);
+    int rc = launch_conv2_bwd(dp2, 1, 0, p2, idx2, p1, w, B, dp1, part, part + (size_t)32 * kC2PartStride, pl, s);
     if (rc) return rc;
     return reduce_to(gw, 25000, part, pl.c2w_split, kC2PartStride, s) ||
            reduce_to(gb, 50, part + 25024, pl.c2w_split, kC2PartStride, s);

@@ -34,7 +34,7 @@ constexpr int kTileA = kBM * kBK * 4, kTileB = kBN * kBK * 4;            // 16,3
 constexpr int kStageBytes = 2 * kTileA + 2 * kTileB;                      // hi + lo of both = 49,152 B
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 static_assert(3 * kStages * 8 + 4 * 8 + 8 <= 256, "barrier area");
-constexpr int kTmemCols = 128;        // two 64-column accumulators (ping-pong)
+constexpr int kTmemCols = 256;        // two (64 main + 64 small-term) accumulators (ping-pong)
 constexpr int kDrain = 8;            // k-blocks (K = 256) accumulated in TMEM before the tile is folded into fp32 registers
 constexpr int kDrainLag = 2;         // the splitters fold group g while they are already 2 k-blocks into group g+1
 
@@ -73,42 +73,41 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
                  ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
                  : "memory");
 }
-// K-major, 128-byte swizzle shared-memory matrix descriptor (LBO = 1, SBO = 8 rows x 128 B, version 1).
-__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-    d |= (uint64_t)1 << 16;                 // leading byte offset (unused for swizzled K-major): 1
-    d |= (uint64_t)(1024 >> 4) << 32;       // stride byte offset: next group of 8 rows
-    d |= (uint64_t)1 << 46;                 // descriptor version (Blackwell)
-    d |= (uint64_t)2 << 61;                 // layout: SWIZZLE_128B
-    return d;
-}
+// Shared-memory matrix descriptors are passed to the MMA as their two 32-bit words:
+//   lo = (start address >> 4) | (LBO >> 4) << 16        hi = (SBO >> 4) | 1 << 14 (version) | layout << 29
+// K-major, 128-byte swizzle (layout 2): rows of 128 B = 32 fp32 along K, LBO unused (1), SBO = 8 rows x 128 B.
 // MN-major operand of 32-bit elements: the only layout the TF32 MMA accepts is the 128-byte swizzle with a
-// 32-BYTE atom (UMMA layout type 1, TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): rows of 128 B = 32 contiguous
-// M/N elements, the four 32-byte units of a row XOR-permuted by (k-row % 4); an atom is 4 k-rows (512 B, SBO);
-// 32-element chunks along M/N are `chunk_bytes` apart (LBO).
-__device__ __forceinline__ uint64_t umma_desc_mn_sw128_32b(uint32_t saddr, uint32_t chunk_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-    d |= (uint64_t)((chunk_bytes >> 4) & 0x3FFF) << 16;
-    d |= (uint64_t)(512 >> 4) << 32;
-    d |= (uint64_t)1 << 46;
-    d |= (uint64_t)1 << 61;
-    return d;
-}
+// 32-BYTE atom (layout 1, TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): rows of 128 B = 32 contiguous M/N elements,
+// the four 32-byte units of a row XOR-permuted by (k-row % 4); an atom is 4 k-rows (SBO = 512 B); 32-element
+// chunks along M/N are LBO apart.
+// K-major without swizzle (layout 0, tc_conv*.cuh): core matrix = 8 rows x 16 B (contiguous 128 B); LBO = distance
+// between the two 16-byte K chunks of a k-step, SBO = distance between consecutive groups of 8 rows.
 // Instruction descriptor: D = F32, A = B = TF32, M x N tile; a_mn / b_mn = 1 for an MN-major operand.
 __host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N, int a_mn = 0, int b_mn = 0) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+// Warp-uniform issue: the whole warp executes the call with identical operands (so they can live in uniform
+// registers) and `leader` (from elect_one()) is non-zero in exactly one lane, which issues the instruction.
+// Descriptors are passed as their two 32-bit words.
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred;
+}
+__device__ __forceinline__ void umma_tf32_u(uint32_t d_tmem, uint32_t a_lo32, uint32_t a_hi32, uint32_t b_lo32,
+                                            uint32_t b_hi32, uint32_t idesc, uint32_t acc, uint32_t leader) {
+    const uint64_t ad = ((uint64_t)a_hi32 << 32) | a_lo32, bd = ((uint64_t)b_hi32 << 32) | b_lo32;
+    asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+                 "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(ad), "l"(bd), "r"(idesc), "r"(acc), "r"(leader)
                  : "memory");
 }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+__device__ __forceinline__ void umma_commit_u(uint32_t bar, uint32_t leader) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t"
+                 "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+                 ::"r"(bar), "r"(leader)
+                 : "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -201,36 +200,43 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_tf32(kBM, kBN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-            for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % kStages, ph = (kb / kStages) & 1;
-                const int grp = kb / kDrain, buf = grp & 1, kin = kb % kDrain;
-                if (kin == 0 && grp >= 2) {   // this accumulator was last used by group grp-2: wait until it has been folded
-                    mbar_wait(smem_u32(&acc_empty[buf]), ((grp >> 1) - 1) & 1);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                }
-                const uint32_t tmem_acc = tmem_d + buf * kBN;
-                mbar_wait(smem_u32(&split_full[s]), ph);
+        // ===== MMA issuer.  The WHOLE warp runs the loop so that every operand is warp-uniform (descriptors stay in
+        // uniform registers, ~3 instructions per MMA instead of a 14-instruction broadcast sequence); one elected
+        // lane issues.  Two MMAs per k-slice: B_lo lies right behind B_hi in the stage, so one N = 2*kBN MMA forms
+        //   A_hi . [B_hi ; B_lo]^T  -> columns [0,kBN) += hi.hi, columns [kBN,2kBN) += hi.lo
+        // with a single read of A_hi, and  A_lo . B_hi^T  adds lo.hi to the second half.  The small terms have their
+        // own accumulator (fewer truncating accumulations into the main one); the drain adds the halves. =====
+        const uint32_t leader = elect_one();
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem_d, 0);
+        constexpr uint32_t idesc2 = umma_idesc_tf32(kBM, 2 * kBN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+        constexpr uint32_t idesc1 = umma_idesc_tf32(kBM, kBN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+        // descriptor words (see the layout notes above): hi = SBO | version | layout, lo = addr | LBO
+        constexpr uint32_t kHiK = (1024u >> 4) | (1u << 14) | (2u << 29), kHiMN = (512u >> 4) | (1u << 14) | (1u << 29);
+        constexpr uint32_t kLboK = 1u << 16, kLboMN = (4096u >> 4) << 16;
+        constexpr uint32_t a_hi32 = A_MN ? kHiMN : kHiK, b_hi32 = B_MN ? kHiMN : kHiK;
+        constexpr uint32_t a_lbo = A_MN ? kLboMN : kLboK, b_lbo = B_MN ? kLboMN : kLboK;
+        // 8 fp32 along K: 32 B inside the swizzle row (K-major) / one 1024-B atom of 8 k-rows (MN-major), in 16-B units
+        constexpr uint32_t a_step = A_MN ? 64 : 2, b_step = B_MN ? 64 : 2;
+        const uint32_t base16 = smem_u32(smem) >> 4;
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % kStages, ph = (kb / kStages) & 1;
+            const int grp = kb / kDrain, buf = grp & 1, kin = kb % kDrain;
+            if (kin == 0 && grp >= 2) {   // this accumulator was last used by group grp-2: wait until it has been folded
+                mbar_wait(smem_u32(&acc_empty[buf]), ((grp >> 1) - 1) & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t a_hi = smem_u32(smem + s * kStageBytes), a_lo = a_hi + kTileA;
-                const uint32_t b_hi = a_hi + 2 * kTileA, b_lo = b_hi + kTileB;
-#pragma unroll
-                for (int kk = 0; kk < kBK / 8; ++kk) {
-                    // 8 fp32 along K: 32 B inside the swizzle row (K-major) / one 1024-B atom of 8 k-rows (MN-major)
-                    const uint32_t aoff = A_MN ? kk * 1024 : kk * 32, boff = B_MN ? kk * 1024 : kk * 32;
-                    const uint64_t dah = A_MN ? umma_desc_mn_sw128_32b(a_hi + aoff, 4096) : umma_desc_k_sw128(a_hi + aoff);
-                    const uint64_t dal = A_MN ? umma_desc_mn_sw128_32b(a_lo + aoff, 4096) : umma_desc_k_sw128(a_lo + aoff);
-                    const uint64_t dbh = B_MN ? umma_desc_mn_sw128_32b(b_hi + boff, 4096) : umma_desc_k_sw128(b_hi + boff);
-                    const uint64_t dbl = B_MN ? umma_desc_mn_sw128_32b(b_lo + boff, 4096) : umma_desc_k_sw128(b_lo + boff);
-                    umma_tf32(tmem_acc, dal, dbh, idesc, (kin | kk) ? 1u : 0u);   // small terms first
-                    umma_tf32(tmem_acc, dah, dbl, idesc, 1u);
-                    umma_tf32(tmem_acc, dah, dbh, idesc, 1u);
-                }
-                umma_commit(smem_u32(&empty[s]));          // stage free once these MMAs have read it
-                if (kin == kDrain - 1 || kb == nkb - 1) umma_commit(smem_u32(&acc_full[buf]));  // group complete
             }
+            const uint32_t tmem_acc = tm + buf * 2 * kBN;
+            mbar_wait(smem_u32(&split_full[s]), ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t a_hi = base16 + s * (kStageBytes >> 4), a_lo = a_hi + (kTileA >> 4), b_hi = a_hi + (2 * kTileA >> 4);
+#pragma unroll
+            for (int kk = 0; kk < kBK / 8; ++kk) {
+                const uint32_t db = (b_hi + kk * b_step) | b_lbo;
+                umma_tf32_u(tmem_acc, (a_hi + kk * a_step) | a_lbo, a_hi32, db, b_hi32, idesc2, (kin | kk) ? 1u : 0u, leader);
+                umma_tf32_u(tmem_acc + kBN, (a_lo + kk * a_step) | a_lbo, a_hi32, db, b_hi32, idesc1, 1u, leader);
+            }
+            umma_commit_u(smem_u32(&empty[s]), leader);          // stage free once these MMAs have read it
+            if (kin == kDrain - 1 || kb == nkb - 1) umma_commit_u(smem_u32(&acc_full[buf]), leader);  // group complete
         }
     } else {
         // ===== splitters (warps 2-5, 128 threads), then epilogue =====
@@ -245,11 +251,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
             for (int c = 0; c < kBN / 32; ++c) {
-                uint32_t r[32];
-                tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + buf * kBN + c * 32, r);
+                uint32_t r[32], r2[32];
+                tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + buf * 2 * kBN + c * 32, r);         // hi.hi
+                tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + buf * 2 * kBN + kBN + c * 32, r2);  // hi.lo + lo.hi
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-                for (int j = 0; j < 32; ++j) acc[c * 32 + j] += __uint_as_float(r[j]);
+                for (int j = 0; j < 32; ++j) acc[c * 32 + j] += __uint_as_float(r[j]) + __uint_as_float(r2[j]);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             mbar_arrive(smem_u32(&acc_empty[buf]));

@@ -64,8 +64,9 @@ def test_fc_backward_tensor_core_path_matches_fp64(B):
 
 @pytest.mark.parametrize("B", [1, 2, 63, 64, 300, 1000])
 def test_conv2_implicit_gemm_tensor_core_path_matches_oracle(B):
-    """conv2 + ReLU + pool as a tcgen05 implicit GEMM (im2col built in shared memory) against float64, and its
-    arg-max map against the fp32 SIMT kernel wherever the window maximum is not a near-tie."""
+    """conv2 + ReLU + pool as a tcgen05 shifted-window implicit GEMM against float64, and its arg-max map against
+    the fp32 SIMT kernel wherever the window maximum is not a near-tie.  B=300 and 1000 make the persistent CTAs
+    walk several image pairs (double-buffered staging / accumulators)."""
     import numpy as np
     import torch.nn.functional as F
     from oracle import mnist_oracle as mo
@@ -77,11 +78,13 @@ def test_conv2_implicit_gemm_tensor_core_path_matches_oracle(B):
     w, b = params["conv2.weight"], params["conv2.bias"]
     d = {"p1": p1.to(DEV), "w": w.to(DEV), "b": b.to(DEV)}
     outs = {}
+    scratch = torch.empty(L.b200mnist_conv2_fwd_tc_scratch_bytes(), dtype=torch.uint8, device=DEV)
     for name, fn in (("tc", L.b200mnist_conv2_relu_pool_fwd_tc), ("simt", L.b200mnist_conv2_relu_pool_fwd)):
         out = torch.full((B, 50, 4, 4), 7.0, device=DEV)
         idx = torch.full((B, 50, 4, 4), 9, dtype=torch.uint8, device=DEV)
+        extra = (scratch.data_ptr(),) if name == "tc" else ()
         _cabi.check(fn(d["p1"].data_ptr(), d["w"].data_ptr(), d["b"].data_ptr(), out.data_ptr(), idx.data_ptr(), B,
-                       torch.cuda.current_stream().cuda_stream), name)
+                       *extra, torch.cuda.current_stream().cuda_stream), name)
         torch.cuda.synchronize()
         outs[name] = (out.cpu(), idx.cpu())
     c = F.relu(F.conv2d(p1.double(), w.double(), b.double()))
@@ -92,3 +95,54 @@ def test_conv2_implicit_gemm_tensor_core_path_matches_oracle(B):
     clear = ((top2[..., 0] - top2[..., 1]) > 1e-5) & (top2[..., 0] > 1e-5)
     assert np.array_equal(outs["tc"][1].numpy()[clear.numpy()], win.argmax(-1).numpy()[clear.numpy()])
     assert np.array_equal(outs["tc"][1].numpy()[clear.numpy()], outs["simt"][1].numpy()[clear.numpy()])
+
+
+@pytest.mark.parametrize("B", [1, 2, 3, 64, 75, 300])
+def test_conv2_backward_tensor_core_paths_match_float64(B, monkeypatch):
+    """conv2 backward with the data gradient (GEMM + col2im epilogue) and/or the weight gradient (one MMA per
+    hi/lo quartet, fp32 folds every 8 images) on tcgen05, and with the fp32 SIMT kernel: all four combinations
+    against float64 autograd formulas on the same arg-max map.  Odd B leaves half an image pair empty, B=75/300
+    make the persistent CTAs walk several tiles (double-buffered operands, patches, accumulators, drains)."""
+    import torch.nn.functional as F
+    from oracle import mnist_oracle as mo
+    from pytorch_operator_b200 import _cabi
+    L = _cabi.lib()
+    params = mo.init_params(3)
+    g = torch.Generator().manual_seed(900 + B)
+    p1 = torch.relu(torch.randn(B, 20, 12, 12, generator=g)).to(DEV)
+    w, b = params["conv2.weight"].to(DEV), params["conv2.bias"].to(DEV)
+    dp2 = torch.randn(B, 50, 4, 4, generator=g).to(DEV)
+    s = torch.cuda.current_stream().cuda_stream
+    p2 = torch.empty(B, 50, 4, 4, device=DEV)
+    i2 = torch.empty(B, 50, 4, 4, dtype=torch.uint8, device=DEV)
+    _cabi.check(L.b200mnist_conv2_relu_pool_fwd(p1.data_ptr(), w.data_ptr(), b.data_ptr(), p2.data_ptr(), i2.data_ptr(), B, s), "fwd")
+    # float64 reference on the kernel's own arg-max map: dconv2 = unpool(dp2 * [p2 > 0])
+    dc2 = torch.zeros(B, 50, 8, 8, dtype=torch.float64, device=DEV)
+    py, px = torch.meshgrid(torch.arange(4, device=DEV), torch.arange(4, device=DEV), indexing="ij")
+    oy = (2 * py)[None, None] + (i2.long() >> 1)
+    ox = (2 * px)[None, None] + (i2.long() & 1)
+    bi = torch.arange(B, device=DEV)[:, None, None, None].expand_as(oy)
+    ci = torch.arange(50, device=DEV)[None, :, None, None].expand_as(oy)
+    dc2[bi, ci, oy, ox] = torch.where(p2 > 0, dp2, torch.zeros_like(dp2)).double()
+    ref_dp1 = F.conv_transpose2d(dc2, w.double())
+    ref_gw = torch.nn.grad.conv2d_weight(p1.double(), w.shape, dc2)
+    ref_gb = dc2.sum((0, 2, 3))
+    scratch = torch.empty(L.b200mnist_conv2_bwd_scratch_bytes(B), dtype=torch.uint8, device=DEV)
+    counts = {}
+    for dg, wg in (("0", "0"), ("1", "0"), ("0", "1"), ("1", "1")):
+        monkeypatch.setenv("B200MNIST_CONV2_DGRAD_TC", dg)
+        monkeypatch.setenv("B200MNIST_CONV2_WGRAD_TC", wg)
+        gw = torch.full((50, 20, 5, 5), 7.0, device=DEV)
+        gb = torch.full((50,), 7.0, device=DEV)
+        dp1 = torch.full((B, 20, 12, 12), 7.0, device=DEV)
+        n0 = L.b200mnist_launch_count()
+        _cabi.check(L.b200mnist_conv2_bwd(dp2.data_ptr(), p2.data_ptr(), i2.data_ptr(), p1.data_ptr(), w.data_ptr(), B,
+                                          gw.data_ptr(), gb.data_ptr(), dp1.data_ptr(), scratch.data_ptr(), s), dg + wg)
+        torch.cuda.synchronize()
+        counts[dg + wg] = L.b200mnist_launch_count() - n0
+        what = f"dgrad tc={dg} wgrad tc={wg} B={B}"
+        assert_close(dp1.cpu().numpy(), ref_dp1.cpu().numpy(), rtol=RTOL, what="dp1 " + what)
+        assert_close(gw.cpu().numpy(), ref_gw.cpu().numpy(), rtol=RTOL, what="gw " + what)
+        assert_close(gb.cpu().numpy(), ref_gb.cpu().numpy(), rtol=RTOL, what="gb " + what)
+    # merged SIMT launch -> (weight split + dgrad GEMM + SIMT wgrad) / (tcgen05 wgrad + SIMT dgrad) / (split + both GEMMs)
+    assert [counts[k] - counts["00"] for k in ("10", "01", "11")] == [2, 1, 2]
