@@ -43,6 +43,15 @@ KERNEL_WORK = {
     "fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)": (805_000, 2000 * 2 + 3200 + 3200 + 2000 + 40, 3_220_000),
     "conv2 backward (wgrad + dgrad)": (3_200_000, 3200 + 3200 + 800 + 11520 + 11520, 200_200),
     "conv1 wgrad": (288_000, 3136 + 11520 + 11520 + 2880, 2080),
+    # large batches (>= 1024): conv2 on tcgen05, forward / data gradient / weight gradient as separate launches
+    "conv2_relu_pool_fwd (tcgen05 3xTF32 shifted-window GEMM)": (1_600_000, 11520 + 3200 + 800, 100_200 + 256_000),
+    "conv2 dgrad (tcgen05 3xTF32 GEMM + col2im)": (1_600_000, 3200 + 3200 + 800 + 11520, 229_376),
+    "conv2 wgrad (tcgen05 3xTF32, all four hi/lo products per MMA)": (1_600_000, 3200 + 3200 + 800 + 11520,
+                                                                     29 * 25088 * 4),
+    "conv2 wgrad": (1_600_000, 3200 + 3200 + 800 + 11520, 32 * 25088 * 4),
+    "conv2 dgrad": (1_600_000, 3200 + 3200 + 800 + 11520, 100_000),
+    "conv2 weight split (hi/lo)": (0, 0, 100_000 + 256_000),
+    "conv2 dgrad weight split (hi/lo)": (0, 0, 100_000 + 229_376),
     "fc1 forward gemm (tcgen05 3xTF32)": (400_000, 3200 + 2000, 1_602_000),
     "fc1 dgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_600_000),
     "fc1 wgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_602_000),
@@ -383,7 +392,8 @@ def main():
     roof.update({"traffic": load_traffic(B).get(top), "kernel": top, "kernel_us": kern_us[top], "peak_source": peaks["source"] +
                  " (MEASURED_PEAKS.json burst bf16 / copy bandwidth)", "algorithmic_flops_per_launch": flops,
                  "algorithmic_bytes_per_launch": nbytes,
-                 "note": ("tcgen05 3xTF32 kernel: algorithmic (fp32-equivalent) FLOPs, 3 MMA passes per product"
+                 "note": ("tcgen05 3xTF32 kernel: algorithmic (fp32-equivalent) FLOPs of the dense product against the "
+                          "bf16 tensor peak; the MMAs issued are 2-4x that (hi/lo products) at TF32 rate (half of bf16)"
                           if "tcgen05" in top else
                           "fp32 SIMT (FFMA2) kernel -- 1e-5 parity rules out single-pass TF32/bf16 MMA; at this batch the "
                           "kernel is latency/occupancy bound (see profiles/), so both roofline fractions are low by construction")})

@@ -743,7 +743,9 @@ int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, 
                         float *gw, float *gb, float *dp1, void *scratch, void *stream) {
     if (!dp2 || !p2 || !idx2 || !p1 || !w || !gw || !gb || !dp1 || !scratch) return fail_arg(1, "null pointer argument");
     if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
-    if (!aligned16(p1) || !aligned16(w) || !aligned16(scratch)) return fail_arg(3, "p1/w/scratch must be 16-byte aligned");
+    if (!aligned16(p1) || !aligned16(w) || !aligned16(scratch) || !aligned16(dp2) || !aligned16(p2) ||
+        (reinterpret_cast<uintptr_t>(idx2) & 3u))
+        return fail_arg(3, "dp2/p2/p1/w/scratch must be 16-byte aligned and idx2 4-byte aligned");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const Plan pl = make_plan(B);
     float *part = static_cast<float *>(scratch);
