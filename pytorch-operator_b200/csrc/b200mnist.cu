@@ -122,7 +122,8 @@ Plan make_plan(int B) {
     p.fc2w_rows = ceil_div(B, p.fc2w_split);
     p.fc2w_split = ceil_div(B, p.fc2w_rows);
     p.c2w_split = clampi(ceil_div(B, 2), 1, 32);
-    p.c1w_split = clampi(B <= 64 ? B : B / 2, 1, kMaxGradSplit);  // small B: one image per CTA; large B: fill the GPU
+    // small B: one image per CTA; large B: 222 x 2 channel halves = 444 CTAs = exactly one wave at 3 CTAs/SM
+    p.c1w_split = clampi(B <= 64 ? B : B / 2, 1, 222);
     // conv2 backward runs 2 CTAs/SM: 5*c2w_split weight-gradient CTAs + 5*c2dg_gx data-gradient CTAs <= 296
     p.c2dg_gx = clampi(B, 1, (296 - 5 * p.c2w_split) / 5);
     // tuning overrides (development only): B200MNIST_PLAN="fc1_split,dg_split,c2w_split,c2dg_gx" (0 = keep)
@@ -204,7 +205,9 @@ int check_step_args(const void *params, const void *x, const void *target, int B
 
 // ---- launches of the individual stages ----
 int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out, uint8_t *idx, int B, cudaStream_t s) {
-    CHECK_PDL(launch_pdl(conv1_relu_pool_fwd_kernel, dim3(B, 20 / kC1ChPerCta), dim3(kC1Threads), 0, s, x, w, b, out, idx, B),
+    // small batches: one CTA per (image, 4-channel group) fills the GPU; large ones: one CTA per image, all groups
+    CHECK_PDL(launch_pdl(conv1_relu_pool_fwd_kernel, dim3(B, B >= 1024 ? 1 : 20 / kC1ChPerCta), dim3(kC1Threads), 0, s, x, w, b,
+                         out, idx, B),
               "conv1_relu_pool_fwd", s);
     return 0;
 }

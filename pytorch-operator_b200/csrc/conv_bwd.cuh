@@ -328,25 +328,34 @@ conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, c
     const int ky = lane / 5, kx = lane - ky * 5;
     const int tap = lane < 25 ? ky * 28 + kx : 0;
     float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
-    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    // One image ahead: the next image's pixels and gradient windows are in flight while this one's list is walked
+    // (with several images per CTA the loop is otherwise one global-memory round trip per image).
+    float gl[5], gl_n[5];
+    int ol[5], ol_n[5];
+    float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), xv_n = xv;
+    auto fetch = [&](int b, float (&g)[5], int (&o)[5], float4 &xq) {
         const size_t base = ((size_t)b * 20 + c) * 144;
-        float gl[5];
-        int ol[5];
-        float4 xv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (tid < kXElems / 4) xv = __ldg(reinterpret_cast<const float4 *>(x + (size_t)b * kXElems) + tid);
+        if (tid < kXElems / 4) xq = __ldg(reinterpret_cast<const float4 *>(x + (size_t)b * kXElems) + tid);
 #pragma unroll
         for (int j = 0; j < 5; ++j) {
             const int wl = j * 32 + lane;
-            gl[j] = 0.f;
-            ol[j] = 0;
+            g[j] = 0.f;
+            o[j] = 0;
             if (wl < 144) {
                 const float pv = __ldcg(p1 + base + wl);
                 const float gv = __ldcg(dp1 + base + wl);
                 const int q = i1[base + wl];
-                gl[j] = pv > 0.f ? gv : 0.f;
-                ol[j] = (2 * (wl / 12) + (q >> 1)) * 28 + 2 * (wl % 12) + (q & 1);
+                g[j] = pv > 0.f ? gv : 0.f;
+                o[j] = (2 * (wl / 12) + (q >> 1)) * 28 + 2 * (wl % 12) + (q & 1);
             }
         }
+    };
+    if ((int)blockIdx.x < B) fetch(blockIdx.x, gl_n, ol_n, xv_n);
+    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+#pragma unroll
+        for (int j = 0; j < 5; ++j) { gl[j] = gl_n[j]; ol[j] = ol_n[j]; }
+        xv = xv_n;
+        if (b + (int)gridDim.x < B) fetch(b + gridDim.x, gl_n, ol_n, xv_n);
         __syncthreads();  // previous image's readers of xs / lst are done
         if (tid < kXElems / 4) reinterpret_cast<float4 *>(xs)[tid] = xv;
         int n = 0;

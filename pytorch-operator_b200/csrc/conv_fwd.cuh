@@ -9,9 +9,11 @@ namespace b200mnist {
 
 // ---------------------------------------------------------------------------------
 // conv1: 1 -> 20 channels on 28x28 (K = 25 per output: not a contraction worth a tensor
-// core).  One CTA = one image x 4 output channels; the 28x28 image is staged once in
+// core).  One CTA = one image x groups of 4 output channels (gridDim.y = 5: one group per CTA,
+// the small-batch shape that fills the GPU; gridDim.y = 1: all five groups in turn, which at
+// large batch amortises the image staging and the patch load); the 28x28 image is staged once in
 // shared memory, each thread owns one pooled pixel: its 6x6 input patch sits in registers
-// and is reused for the 4 conv outputs of the window and for all 4 channels (weights are
+// and is reused for the 4 conv outputs of the window and for all channels (weights are
 // warp-uniform LDS.128 broadcasts of [tap][4 channels]).  ReLU, max and arg-max are taken in
 // registers, so the 24x24 conv map never exists in memory.
 // ---------------------------------------------------------------------------------
@@ -24,14 +26,16 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
 
     pdl_wait();
     __shared__ __align__(16) float xs[kXElems];
-    __shared__ __align__(16) float ws[25 * kC1ChPerCta];
-    __shared__ float bs[kC1ChPerCta];
-    const int b = blockIdx.x, c0 = blockIdx.y * kC1ChPerCta, t = threadIdx.x;
+    __shared__ __align__(16) float ws[5][25 * kC1ChPerCta];
+    __shared__ float bs[20];
+    const int b = blockIdx.x, t = threadIdx.x;
     const float4 *xg = reinterpret_cast<const float4 *>(x + (size_t)b * kXElems);
     float4 xv0 = __ldg(xg + t), xv1 = make_float4(0.f, 0.f, 0.f, 0.f);
     if (t + kC1Threads < kXElems / 4) xv1 = __ldg(xg + t + kC1Threads);
-    if (t < 25 * kC1ChPerCta) ws[(t % 25) * kC1ChPerCta + t / 25] = __ldg(w + c0 * 25 + t);
-    if (t < kC1ChPerCta) bs[t] = __ldg(bias + c0 + t);
+    for (int cg = blockIdx.y; cg < 5; cg += gridDim.y) {   // this CTA's channel groups: [tap][4 channels] each
+        if (t < 25 * kC1ChPerCta) ws[cg][(t % 25) * kC1ChPerCta + t / 25] = __ldg(w + cg * kC1ChPerCta * 25 + t);
+        if (t < kC1ChPerCta) bs[cg * kC1ChPerCta + t] = __ldg(bias + cg * kC1ChPerCta + t);
+    }
     reinterpret_cast<float4 *>(xs)[t] = xv0;
     if (t + kC1Threads < kXElems / 4) reinterpret_cast<float4 *>(xs)[t + kC1Threads] = xv1;
     __syncthreads();
@@ -46,16 +50,18 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
             patch[r][2 * j] = v.x;
             patch[r][2 * j + 1] = v.y;
         }
+    for (int cg = blockIdx.y; cg < 5; cg += gridDim.y) {
+    const int c0 = cg * kC1ChPerCta;
     float2 acc[2][4];  // [channel pair][window slot]
 #pragma unroll
     for (int cp = 0; cp < 2; ++cp)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[cp][q] = make_float2(bs[2 * cp], bs[2 * cp + 1]);
+        for (int q = 0; q < 4; ++q) acc[cp][q] = make_float2(bs[c0 + 2 * cp], bs[c0 + 2 * cp + 1]);
 #pragma unroll
     for (int ky = 0; ky < 5; ++ky)
 #pragma unroll
         for (int kx = 0; kx < 5; ++kx) {
-            const float4 w4 = *reinterpret_cast<const float4 *>(&ws[(ky * 5 + kx) * kC1ChPerCta]);
+            const float4 w4 = *reinterpret_cast<const float4 *>(&ws[cg][(ky * 5 + kx) * kC1ChPerCta]);
             const float2 wp[2] = {make_float2(w4.x, w4.y), make_float2(w4.z, w4.w)};
             const float2 p00 = make_float2(patch[ky][kx], patch[ky][kx]);
             const float2 p01 = make_float2(patch[ky][kx + 1], patch[ky][kx + 1]);
@@ -82,6 +88,7 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
         const size_t o = ((size_t)b * 20 + c0 + c) * 144 + t;
         out[o] = fmaxf(best, 0.f);
         idx[o] = (uint8_t)bi;
+    }
     }
 }
 

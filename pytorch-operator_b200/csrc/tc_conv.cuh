@@ -11,8 +11,10 @@
 // map reads input position (y+ky, x+kx), so the A operand of kernel offset (ky,kx) is THE SAME staged planes with
 // the descriptor's start address advanced by (ky*24 + kx)*16 bytes.  One hi/lo split per input value (3xTF32)
 // instead of one per im2col entry (25x fewer), no gather, and the MMA operands are read from shared memory only by
-// the tensor core.  K = 20 is two and a half k-steps of 8: the third step pairs chunk 4 with a shared plane of
-// zeros (its LBO simply points there), so nothing is padded.
+// the tensor core.  K = 20 is two and a half k-steps of 8: the half steps (channels 16..19) of two consecutive taps
+// share one MMA -- its two 16-byte K chunks are chunk 4 at tap o and chunk 4 at tap o+1 (LBO = the distance between
+// the two windows, resp. weight blocks) -- and the odd tap out pairs with a plane of zeros, so nothing is padded:
+// 63 k-steps instead of 75.
 // The weights are pre-split (hi/lo) and pre-arranged per (N tile, offset) by conv2_weight_split_kernel; all 25
 // offsets of a tile (NT=32: 128 KB) are loaded once per CTA with five bulk async copies and stay resident while a
 // persistent CTA walks image pairs: double-buffered A staging (stager warps), MMA issue (one warp, one elected
@@ -131,7 +133,7 @@ conv2_fwd_win_kernel(const float *__restrict__ in, const float *__restrict__ w2s
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer: 25 offsets x 3 k-steps x 2 MMAs.  The WHOLE warp runs the loop so that every operand
+        // ===== MMA issuer: 63 k-steps (25 taps x 2 + 13 shared half steps) x 2 MMAs.  The WHOLE warp runs the loop so that every operand
         // is warp-uniform (descriptors live in uniform registers, ~3 instructions per MMA); one elected lane issues.
         const uint32_t leader = elect_one();
         const uint32_t tm = __shfl_sync(0xffffffffu, tmem_d, 0);
@@ -154,14 +156,24 @@ conv2_fwd_win_kernel(const float *__restrict__ in, const float *__restrict__ w2s
                 const uint32_t shift = (uint32_t)((o / 5) * 24 + (o % 5));
                 const uint32_t b = w0 + o * kWB;
 #pragma unroll
-                for (int ks = 0; ks < 3; ++ks) {
-                    // k-step 2 = chunk 4 + the zero plane / zero block (its LBO points there)
+                for (int ks = 0; ks < 2; ++ks) {      // channels 0..7 and 8..15 of this tap
                     const uint32_t ah = a_hi + ks * 2 * kP, al = a_lo + ks * 2 * kP, bc = b + ks * 2 * kWC;
-                    const uint32_t dah = (ah + shift) | ((ks < 2 ? kP : az - ah) << 16);
-                    const uint32_t dal = (al + shift) | ((ks < 2 ? kP : az - al) << 16);
-                    const uint32_t db = bc | ((ks < 2 ? kWC : wz - bc) << 16);
-                    umma_tf32_u(d, dah, kAHi, db, kBHi, idesc64, (o | ks) ? 1u : 0u, leader);   // hi.hi | hi.lo
-                    umma_tf32_u(d + NT, dal, kAHi, db, kBHi, idesc32, 1u, leader);               // lo.hi
+                    const uint32_t db = bc | (kWC << 16);
+                    umma_tf32_u(d, (ah + shift) | (kP << 16), kAHi, db, kBHi, idesc64, (o | ks) ? 1u : 0u, leader);   // hi.hi | hi.lo
+                    umma_tf32_u(d + NT, (al + shift) | (kP << 16), kAHi, db, kBHi, idesc32, 1u, leader);              // lo.hi
+                }
+                // channels 16..19 are half a k-step: pair this tap's chunk 4 with the previous tap's (the second
+                // 16-byte K chunk may lie anywhere: LBO = distance between the two taps' windows / weight blocks);
+                // the odd tap out (24) pairs with the plane / block of zeros
+                if ((o & 1) || o == 24) {
+                    const int o0 = o == 24 ? 24 : o - 1;
+                    const uint32_t sh0 = (uint32_t)((o0 / 5) * 24 + (o0 % 5));
+                    const uint32_t ah = a_hi + 4 * kP + sh0, al = a_lo + 4 * kP + sh0, bc = w0 + o0 * kWB + 4 * kWC;
+                    const uint32_t lbo_ah = o == 24 ? az - (a_hi + 4 * kP) : shift - sh0;
+                    const uint32_t lbo_al = o == 24 ? az - (a_lo + 4 * kP) : shift - sh0;
+                    const uint32_t db = bc | ((o == 24 ? wz - bc : kWB) << 16);
+                    umma_tf32_u(d, ah | (lbo_ah << 16), kAHi, db, kBHi, idesc64, 1u, leader);
+                    umma_tf32_u(d + NT, al | (lbo_al << 16), kAHi, db, kBHi, idesc32, 1u, leader);
                 }
             }
             umma_commit_u(smem_u32(&a_empty[buf]), leader);

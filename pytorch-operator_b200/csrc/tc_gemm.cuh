@@ -29,7 +29,8 @@ namespace tc {
 
 constexpr int kBM = 128, kBN = 64, kBK = 32;           // CTA tile; kBK fp32 = one 128-byte swizzle row
 constexpr int kStages = 4;
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;           // warp 0: TMA, warp 1: MMA issuer, warps 2-5: split + drain + epilogue, warps 6-9: split only
+constexpr int kSplitters = 256;
 constexpr int kTileA = kBM * kBK * 4, kTileB = kBN * kBK * 4;            // 16,384 B and 8,192 B
 constexpr int kStageBytes = 2 * kTileA + 2 * kTileB;                      // hi + lo of both = 49,152 B
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
@@ -153,7 +154,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(smem_u32(&raw_full[s]), 1);
-            mbar_init(smem_u32(&split_full[s]), 128);
+            mbar_init(smem_u32(&split_full[s]), kSplitters);
             mbar_init(smem_u32(&empty[s]), 1);
         }
         for (int b = 0; b < 2; ++b) {
@@ -239,8 +240,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             if (kin == kDrain - 1 || kb == nkb - 1) umma_commit_u(smem_u32(&acc_full[buf]), leader);  // group complete
         }
     } else {
-        // ===== splitters (warps 2-5, 128 threads), then epilogue =====
+        // ===== splitters (warps 2-9, 256 threads); warps 2-5 also drain TMEM and run the epilogue =====
         const int t = threadIdx.x - 64;
+        const bool drainer = warp < 6;
         const int q = warp & 3;            // a warp may only touch its own TMEM lane quarter
         float acc[kBN];
 #pragma unroll
@@ -263,7 +265,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         };
         int next_drain = 0;
         for (int kb = 0; kb < nkb; ++kb) {
-            if (next_drain < ngroups && kb >= (next_drain + 1) * kDrain + kDrainLag) drain(next_drain++);
+            if (drainer && next_drain < ngroups && kb >= (next_drain + 1) * kDrain + kDrainLag) drain(next_drain++);
             const int s = kb % kStages, ph = (kb / kStages) & 1;
             mbar_wait(smem_u32(&raw_full[s]), ph);
             uint8_t *st = smem + s * kStageBytes;
@@ -277,20 +279,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
             };
 #pragma unroll
-            for (int j = 0; j < kTileA / 16 / 128; ++j) {
+            for (int j = 0; j < kTileA / 16 / kSplitters; ++j) {
                 uint4 hi, lo;
-                split(ah[t + j * 128], hi, lo);
-                ah[t + j * 128] = hi;
-                al[t + j * 128] = lo;
+                split(ah[t + j * kSplitters], hi, lo);
+                ah[t + j * kSplitters] = hi;
+                al[t + j * kSplitters] = lo;
             }
 #pragma unroll
-            for (int j = 0; j < kTileB / 16 / 128; ++j) {
+            for (int j = 0; j < kTileB / 16 / kSplitters; ++j) {
                 uint4 hi, lo;
-                split(bh[t + j * 128], hi, lo);
-                bh[t + j * 128] = hi;
-                bl[t + j * 128] = lo;
+                split(bh[t + j * kSplitters], hi, lo);
+                bh[t + j * kSplitters] = hi;
+                bl[t + j * kSplitters] = lo;
             }
-            if (ones_cta) asm volatile("bar.sync 1, 128;" ::: "memory");  // the split pass has rewritten every vector of B_hi
+            if (ones_cta) asm volatile("bar.sync 1, 256;" ::: "memory");  // the split pass has rewritten every vector of B_hi
             if (ones_cta && t < kBK) {
                 // column n == N of B (all zeros from the out-of-bounds TMA fill) := 1.0 for this k-block's rows:
                 // MN-major chunk c = (N - n0)/32, k-row t at t*128 B, 32-byte unit ((col/8) ^ (t % 4)), float col%8
@@ -301,10 +303,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the MMA (async proxy)
             mbar_arrive(smem_u32(&split_full[s]));
         }
-        while (next_drain < ngroups) drain(next_drain++);
+        while (drainer && next_drain < ngroups) drain(next_drain++);
         // epilogue: registers -> global
         const int row = m0 + q * 32 + lane;
-        if (row < g.M) {
+        if (drainer && row < g.M) {
 #pragma unroll
             for (int j = 0; j < kBN; ++j) {
                 const int n = n0 + j;
