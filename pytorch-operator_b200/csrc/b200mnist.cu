@@ -142,7 +142,7 @@ Plan make_plan(int B) {
     }
     if (ov[2] > 0) p.c2w_split = clampi(ov[2], 1, 32);
     if (ov[3] > 0) p.c2dg_gx = clampi(ov[3], 1, B);
-    // conv2 backward on the tensor cores: auto from kTcMinBatch up; B200MNIST_CONV2_WGRAD_TC / _DGRAD_TC = 1 / 0 force
+    // conv2 backward on the tensor cores: auto from kTcConvMinBatch up; B200MNIST_CONV2_WGRAD_TC / _DGRAD_TC = 1 / 0 force
     p.c2w_tc = tc_path_enabled("B200MNIST_CONV2_WGRAD_TC", B);
     p.c2dg_tc = tc_path_enabled("B200MNIST_CONV2_DGRAD_TC", B);
     if (p.c2w_tc) p.c2w_split = B < tc::kWgMaxSlices ? B : tc::kWgMaxSlices;
@@ -227,14 +227,17 @@ int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *
               "conv2_relu_pool_fwd (tcgen05 3xTF32 shifted-window GEMM)", s);
     return 0;
 }
-// Which conv2 forward runs inside the fused step: the tensor-core kernel wins from a few hundred images up (B=4096:
-// 141 vs 228 us; B=1024: 44 vs 61 us) and loses at the reference batch (B=64: its 64 CTAs pay the 128 KB weight load
-// and a 150-MMA chain each, 11 vs 9 us), so it switches on together with the tcgen05 fc1 GEMMs at kTcMinBatch.
-// B200MNIST_CONV2_TC=1 / =0 forces it on / off (tests, profiling).
+// Which conv2 kernels run inside the fused step.  Measured step time, tcgen05 conv kernels off / on (tools/
+// sweep_tc_threshold.sh): B=128 96.3 / 94.2 us, B=256 163 / 134 us, B=512 294 / 223 us, B=4096 1.65 / 1.05 ms; at the
+// reference batch (64) they lose (their fixed costs -- TMEM allocation, zero-filled operand planes, 60-130 KB of weights
+// per CTA -- exceed the whole FFMA2 kernel).  So the conv kernels switch on at kTcConvMinBatch; the fc1 GEMMs need
+// M = B large enough to fill 128-row tiles on 148 SMs and switch at kTcMinBatch.
+// B200MNIST_CONV2_TC / _DGRAD_TC / _WGRAD_TC = 1 / 0 force each conv kernel on / off (tests, profiling).
 constexpr int kTcMinBatch = 1024;
+constexpr int kTcConvMinBatch = 256;
 bool tc_path_enabled(const char *env, int B) {   // read at every (uncaptured) launch: a few hundred ns, lets tests toggle it
     const char *e = getenv(env);
-    return (!e || !e[0]) ? B >= kTcMinBatch : e[0] == '1';
+    return (!e || !e[0]) ? B >= kTcConvMinBatch : e[0] == '1';
 }
 bool conv2_tc_enabled(int B) { return tc_path_enabled("B200MNIST_CONV2_TC", B); }
 int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,

@@ -58,6 +58,18 @@ def tie_free_batch(params, B, seed, min_gap=5e-7):
     raise AssertionError("no tie-free batch found")
 
 
+def kink_free_batch(params, B, seed, min_abs=5e-6):
+    """synthetic_batch(B, seed'), with seed' the first seed >= `seed` whose pooled conv2 pre-activations all stay
+    `min_abs` away from zero (oracle.mnist_oracle.relu_kink_gap): the batches on which the 3xTF32 convolution and an
+    fp32 one must agree on every ReLU mask."""
+    from oracle import mnist_oracle as mo
+    for s in range(seed, seed + 200):
+        x, t = mo.synthetic_batch(B, s)
+        if mo.relu_kink_gap(params, x) >= min_abs:
+            return x, t
+    raise AssertionError("no kink-free batch found")
+
+
 def golden_batch(gold, B, step, rank):
     """The batch gen_golden.py used for (step, rank): the seed is stored in the fixture."""
     from oracle import mnist_oracle as mo
