@@ -122,8 +122,8 @@ Plan make_plan(int B) {
     p.fc2w_rows = ceil_div(B, p.fc2w_split);
     p.fc2w_split = ceil_div(B, p.fc2w_rows);
     p.c2w_split = clampi(ceil_div(B, 2), 1, 32);
-    // small B: one image per CTA; large B: 222 x 2 channel halves = 444 CTAs = exactly one wave at 3 CTAs/SM
-    p.c1w_split = clampi(B <= 64 ? B : B / 2, 1, 222);
+    // small B: one image per CTA; large B: 148 x 2 channel halves = 296 CTAs = exactly one wave at 2 CTAs/SM
+    p.c1w_split = clampi(B <= 64 ? B : B / 2, 1, 148);
     // conv2 backward runs 2 CTAs/SM: 5*c2w_split weight-gradient CTAs + 5*c2dg_gx data-gradient CTAs <= 296
     p.c2dg_gx = clampi(B, 1, (296 - 5 * p.c2w_split) / 5);
     // tuning overrides (development only): B200MNIST_PLAN="fc1_split,dg_split,c2w_split,c2dg_gx" (0 = keep)

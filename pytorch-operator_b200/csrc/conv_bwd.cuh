@@ -306,12 +306,13 @@ __global__ void __launch_bounds__(kConvBwdThreads) conv2_bwd_kernel(const Conv2B
 
 // ---------------------------------------------------------------------------------
 // conv1 weight/bias gradient (the input image needs no gradient).  The conv1 output
-// gradient has one non-zero per 2x2 window (pool arg-max) and none where ReLU was inactive,
-// so the sum is taken sparsely.  warp = channel, lane = filter tap (25 active, lane 25 sums
-// the bias gradient).  Per (image, channel) the warp first builds, in shared memory, the
-// compacted list of its non-zero windows as (gradient, input offset) pairs -- 5 independent
-// loads per lane, ballot + popc prefix -- then every lane walks the list: one broadcast
-// LDS.64 for the pair, one LDS for its input pixel, one FMA, four entries in flight.
+// gradient has one non-zero per 2x2 window (the pool arg-max; none where ReLU was inactive),
+// so the sum runs over the 144 pooled windows, not the 576 conv outputs.  warp = channel,
+// lane = window (five windows per lane): the lane keeps its window's (gradient, input offset)
+// in registers and accumulates all 25 taps -- 25 independent FMA chains fed by one LDS each,
+// no list building, no dependent shared-memory round trips -- plus the bias gradient; the
+// 26 per-lane sums are reduced across the warp once, after the CTA's last image.  The next
+// image's pixels and gradient windows are fetched while the current one is accumulated.
 // grid = (batch slices, 2 channel halves); each CTA writes a partial [512 + 64].
 // ---------------------------------------------------------------------------------
 constexpr int kC1wThreads = 320;    // 10 channels x 32 lanes
@@ -323,13 +324,10 @@ conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, c
 
     pdl_wait();
     __shared__ __align__(16) float xs[kXElems];
-    __shared__ __align__(8) float2 lst[10][160];
     const int tid = threadIdx.x, wid = tid >> 5, c = blockIdx.y * 10 + wid, lane = tid & 31;
-    const int ky = lane / 5, kx = lane - ky * 5;
-    const int tap = lane < 25 ? ky * 28 + kx : 0;
-    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
-    // One image ahead: the next image's pixels and gradient windows are in flight while this one's list is walked
-    // (with several images per CTA the loop is otherwise one global-memory round trip per image).
+    float acc[25], accb = 0.f;
+#pragma unroll
+    for (int k = 0; k < 25; ++k) acc[k] = 0.f;
     float gl[5], gl_n[5];
     int ol[5], ol_n[5];
     float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), xv_n = xv;
@@ -356,37 +354,33 @@ conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, c
         for (int j = 0; j < 5; ++j) { gl[j] = gl_n[j]; ol[j] = ol_n[j]; }
         xv = xv_n;
         if (b + (int)gridDim.x < B) fetch(b + gridDim.x, gl_n, ol_n, xv_n);
-        __syncthreads();  // previous image's readers of xs / lst are done
+        __syncthreads();  // previous image's readers of xs are done
         if (tid < kXElems / 4) reinterpret_cast<float4 *>(xs)[tid] = xv;
-        int n = 0;
+        __syncthreads();
 #pragma unroll
         for (int j = 0; j < 5; ++j) {
-            const bool nz = gl[j] != 0.f;
-            const unsigned m = __ballot_sync(0xffffffffu, nz);
-            if (nz) lst[wid][n + __popc(m & ((1u << lane) - 1u))] = make_float2(gl[j], __int_as_float(ol[j]));
-            n += __popc(m);
-        }
-        if (lane < 4) lst[wid][n + lane] = make_float2(0.f, __int_as_float(0));  // pad to a multiple of 4
-        __syncthreads();
-        const float2 *l = lst[wid];
-        if (lane < 25) {
-            for (int i = 0; i < n; i += 4) {
-                const float2 e0 = l[i], e1 = l[i + 1], e2 = l[i + 2], e3 = l[i + 3];
-                acc0 = fmaf(e0.x, xs[__float_as_int(e0.y) + tap], acc0);
-                acc1 = fmaf(e1.x, xs[__float_as_int(e1.y) + tap], acc1);
-                acc2 = fmaf(e2.x, xs[__float_as_int(e2.y) + tap], acc2);
-                acc3 = fmaf(e3.x, xs[__float_as_int(e3.y) + tap], acc3);
-            }
-        } else if (lane == 25) {
-            for (int i = 0; i < n; i += 4) {
-                acc0 += l[i].x; acc1 += l[i + 1].x; acc2 += l[i + 2].x; acc3 += l[i + 3].x;
-            }
+            const float g = gl[j];
+            const float *px = xs + ol[j];
+            accb += g;
+#pragma unroll
+            for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+                for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] = fmaf(g, px[ky * 28 + kx], acc[ky * 5 + kx]);
         }
     }
-    const float acc = (acc0 + acc1) + (acc2 + acc3);
+    float mine = 0.f;   // lane k < 25 ends up with tap k, lane 25 with the bias gradient
+#pragma unroll
+    for (int k = 0; k < 25; ++k) {
+        const float s = warp_sum(acc[k]);
+        if (lane == k) mine = s;
+    }
+    {
+        const float s = warp_sum(accb);
+        if (lane == 25) mine = s;
+    }
     float *po = part + (size_t)blockIdx.x * kC1PartStride;
-    if (lane < 25) po[c * 25 + lane] = acc;
-    else if (lane == 25) po[512 + c] = acc;
+    if (lane < 25) po[c * 25 + lane] = mine;
+    else if (lane == 25) po[512 + c] = mine;
 }
 
 }  // namespace b200mnist
