@@ -55,6 +55,7 @@ KERNEL_WORK = {
     "fc1 forward gemm (tcgen05 3xTF32)": (400_000, 3200 + 2000, 1_602_000),
     "fc1 dgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_600_000),
     "fc1 wgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_602_000),
+    "fc1 wgrad + dgrad gemms (tcgen05 3xTF32, one launch)": (800_000, 2000 + 3200 + 3200, 3_202_000),
     "sgd momentum": (0, 0, 5 * PARAM_BYTES),
     "grad finalize": (0, 0, 2 * 31_080 * 4),
 }

@@ -274,21 +274,23 @@ int launch_fc1_fwd_tc(const float *in, const float *w, const float *bias, float 
     tc::TcGemmArgs a{bias, h, nullptr, B, 500, 800, 500};
     return launch_tc<false, false, tc::kEpiBiasRelu>(ma, mb, a, "fc1 forward gemm (tcgen05 3xTF32)", s);
 }
-// dp2[B,800] = dz1[B,500] . W1[500,800]
-int launch_fc1_dgrad_tc(const float *dz1, const float *w1, float *dp2, int B, cudaStream_t s) {
-    CUtensorMap ma, mb;
-    if (!tc::make_map_kmajor(&ma, dz1, B, 500, 500, tc::kBM) || !tc::make_map_mnmajor(&mb, w1, 500, 800, 800))
+// dp2[B,800] = dz1[B,500] . W1[500,800];  gW1[500,800] = dz1[B,500]^T . p2[B,800], gb1[500] = column sums of dz1:
+// both backward GEMMs of fc1 in one launch (tc::fc1_bwd_tc_kernel)
+int launch_fc1_bwd_tc(const float *dz1, const float *p2, const float *w1, float *gw1, float *gb1, float *dp2, int B,
+                      cudaStream_t s) {
+    CUtensorMap wa, wb, da, db;
+    if (!tc::make_map_mnmajor(&wa, dz1, B, 500, 500) || !tc::make_map_mnmajor(&wb, p2, B, 800, 800) ||
+        !tc::make_map_kmajor(&da, dz1, B, 500, 500, tc::kBM) || !tc::make_map_mnmajor(&db, w1, 500, 800, 800))
         return fail_arg(8, kTmapErr);
-    tc::TcGemmArgs a{nullptr, dp2, nullptr, B, 800, 500, 800};
-    return launch_tc<false, true, tc::kEpiStore>(ma, mb, a, "fc1 dgrad gemm (tcgen05 3xTF32)", s);
-}
-// gW1[500,800] = dz1[B,500]^T . p2[B,800] ; gb1[500] = column sums of dz1
-int launch_fc1_wgrad_tc(const float *dz1, const float *p2, float *gw1, float *gb1, int B, cudaStream_t s) {
-    CUtensorMap ma, mb;
-    if (!tc::make_map_mnmajor(&ma, dz1, B, 500, 500) || !tc::make_map_mnmajor(&mb, p2, B, 800, 800))
-        return fail_arg(8, kTmapErr);
-    tc::TcGemmArgs a{nullptr, gw1, gb1, 500, 800, B, 800};
-    return launch_tc<true, true, tc::kEpiWgrad>(ma, mb, a, "fc1 wgrad gemm (tcgen05 3xTF32)", s);
+    static unsigned long long attr_mask = 0;
+    cudaError_t ea = ensure_dynamic_smem(tc::fc1_bwd_tc_kernel, tc::kSmemBytes, &attr_mask);
+    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(fc1_bwd_tc)");
+    const tc::TcGemmArgs wg{nullptr, gw1, gb1, 500, 800, B, 800}, dg{nullptr, dp2, nullptr, B, 800, 500, 800};
+    const int wg_gx = ceil_div(800 + 1, tc::kBN), n_wg = wg_gx * ceil_div(500, tc::kBM);   // + the bias-gradient column
+    const int dg_gx = ceil_div(800, tc::kBN), n_dg = dg_gx * ceil_div(B, tc::kBM);
+    tc::fc1_bwd_tc_kernel<<<dim3(n_wg + n_dg), tc::kThreads, tc::kSmemBytes, s>>>(wa, wb, wg, da, db, dg, wg_gx, n_wg, dg_gx);
+    CHECK_LAUNCH("fc1 wgrad + dgrad gemms (tcgen05 3xTF32, one launch)", s);
+    return 0;
 }
 // fc1 forward: returns the number of split-K partials left in `part` (0 = `h` is final).
 int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h, float *part, int B, const Plan &pl,
@@ -334,9 +336,8 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
     if (use_tc) {
         a.wg_n = 0;
         a.dg_n = 0;  // the SIMT launch keeps only the (tiny) fc2 weight-gradient role
-        int rc = launch_fc1_wgrad_tc(dz1, p2, gw1, gb1, B, s);
+        int rc = launch_fc1_bwd_tc(dz1, p2, w1, gw1, gb1, dp2_part, B, s);
         if (rc) return rc;
-        if ((rc = launch_fc1_dgrad_tc(dz1, w1, dp2_part, B, s))) return rc;
     }
     CHECK_PDL(launch_pdl(fc_bwd_kernel, dim3(a.wg_n + a.dg_n + a.fc2_gx * pl.fc2w_split), dim3(256), 0, s, a),
               "fc backward (fc1 wgrad + fc1 dgrad + fc2 wgrad)", s);

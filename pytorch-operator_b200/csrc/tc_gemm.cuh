@@ -134,9 +134,8 @@ struct TcGemmArgs {
 
 // A_MN / B_MN: operand is MN-major in global memory (its M / N index is the contiguous one).
 template <bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(kThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-               const TcGemmArgs g) {
+__device__ __forceinline__ void gemm_tc_tile(const CUtensorMap &map_a, const CUtensorMap &map_b, const TcGemmArgs &g,
+                                             const int tile_x, const int tile_y) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     // stage s: [A_hi | A_lo | B_hi | B_lo]; barriers after the last stage
@@ -145,7 +144,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     uint64_t *acc_full = bars + 3 * kStages, *acc_empty = bars + 3 * kStages + 2;   // [2] each
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 3 * kStages + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.y * kBM, n0 = blockIdx.x * kBN;
+    const int m0 = tile_y * kBM, n0 = tile_x * kBN;
     const int nkb = (g.K + kBK - 1) / kBK;
     const int ngroups = (nkb + kDrain - 1) / kDrain;
     // wgrad: the CTA whose N tile contains column N (= 800) carries the injected column of ones
@@ -324,6 +323,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(kTmemCols) : "memory");
+    }
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               const TcGemmArgs g) {
+    gemm_tc_tile<A_MN, B_MN, EPI>(map_a, map_b, g, blockIdx.x, blockIdx.y);
+}
+
+// fc1's two backward GEMMs in ONE launch (they only share dz1): the first n_wg CTAs are weight-gradient tiles
+// (gW1 = dz1^T . p2, K = B: few, long tiles -- 52 CTAs cannot fill 148 SMs on their own), the rest data-gradient
+// tiles (dp2 = dz1 . W1, K = 500: many short ones) that fill the remaining SMs while the long tiles run.
+__global__ void __launch_bounds__(kThreads, 1)
+fc1_bwd_tc_kernel(const __grid_constant__ CUtensorMap wg_a, const __grid_constant__ CUtensorMap wg_b, const TcGemmArgs wg,
+                  const __grid_constant__ CUtensorMap dg_a, const __grid_constant__ CUtensorMap dg_b, const TcGemmArgs dg,
+                  const int wg_gx, const int n_wg, const int dg_gx) {
+    int b = blockIdx.x;
+    if (b < n_wg) {
+        gemm_tc_tile<true, true, kEpiWgrad>(wg_a, wg_b, wg, b % wg_gx, b / wg_gx);
+    } else {
+        b -= n_wg;
+        gemm_tc_tile<false, true, kEpiStore>(dg_a, dg_b, dg, b % dg_gx, b / dg_gx);
     }
 }
 
