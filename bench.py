@@ -52,6 +52,7 @@ KERNEL_WORK = {
     "conv2 dgrad": (1_600_000, 3200 + 3200 + 800 + 11520, 100_000),
     "conv2 weight split (hi/lo)": (0, 0, 100_000 + 256_000),
     "conv2 dgrad weight split (hi/lo)": (0, 0, 100_000 + 229_376),
+    "conv2 weight split (hi/lo; forward + dgrad operands)": (0, 0, 100_000 + 256_000 + 229_376),
     "fc1 forward gemm (tcgen05 3xTF32)": (400_000, 3200 + 2000, 1_602_000),
     "fc1 dgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_600_000),
     "fc1 wgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_602_000),

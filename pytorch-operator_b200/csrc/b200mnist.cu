@@ -105,6 +105,7 @@ struct Plan {
     int fc2w_split, fc2w_rows;  // fc2 weight-gradient batch split
     int c2w_split;              // conv2 weight-gradient batch split (= number of partials)
     bool c2w_tc, c2dg_tc;       // conv2 weight / data gradient on the tensor cores (tc_conv_bwd.cuh)
+    bool c2_presplit;           // training step: the forward's weight-split launch also builds the data-gradient operand
     int c1w_split;              // conv1 weight-gradient batch split
     int c2dg_gx;                // conv2 data-gradient CTAs per channel tile
 };
@@ -146,6 +147,7 @@ Plan make_plan(int B) {
     p.c2w_tc = tc_path_enabled("B200MNIST_CONV2_WGRAD_TC", B);
     p.c2dg_tc = tc_path_enabled("B200MNIST_CONV2_DGRAD_TC", B);
     if (p.c2w_tc) p.c2w_split = B < tc::kWgMaxSlices ? B : tc::kWgMaxSlices;
+    p.c2_presplit = p.c2dg_tc && tc_path_enabled("B200MNIST_CONV2_TC", B);
     return p;
 }
 
@@ -215,12 +217,16 @@ const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver 
 // conv2 forward on the tensor cores (tcgen05 3xTF32, shifted-window implicit GEMM; tc_conv.cuh).  `w2s` receives the
 // hi/lo-split, operand-ordered copy of conv2.weight (tc::kWnScratchFloats floats), rebuilt on every call.
 int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B, float *w2s,
-                        cudaStream_t s) {
+                        cudaStream_t s, float *wd_also = nullptr) {
     constexpr int NT = 32;
     static unsigned long long attr_mask = 0;
     cudaError_t ea = ensure_dynamic_smem(tc::conv2_fwd_win_kernel<NT>, tc::wn_smem_bytes<NT>(), &attr_mask);
     if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_fwd_win)");
-    CHECK_PDL(launch_pdl(tc::conv2_weight_split_kernel<NT>, dim3(25), dim3(256), 0, s, w, w2s), "conv2 weight split (hi/lo)", s);
+    if (wd_also)
+        CHECK_PDL(launch_pdl(tc::conv2_weight_split_both_kernel, dim3(25 + 4 * tc::kDgChunks), dim3(256), 0, s, w, w2s, wd_also),
+                  "conv2 weight split (hi/lo; forward + dgrad operands)", s);
+    else
+        CHECK_PDL(launch_pdl(tc::conv2_weight_split_kernel<NT>, dim3(25), dim3(256), 0, s, w, w2s), "conv2 weight split (hi/lo)", s);
     const int npairs = (B + 1) / 2;
     CHECK_PDL(launch_pdl(tc::conv2_fwd_win_kernel<NT>, dim3(npairs < 74 ? npairs : 74, 64 / NT), dim3(tc::kWnThreads),
                          (size_t)tc::wn_smem_bytes<NT>(), s, in, (const float *)w2s, b, out, idx, B),
@@ -243,8 +249,8 @@ bool conv2_tc_enabled(int B) { return tc_path_enabled("B200MNIST_CONV2_TC", B); 
 int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
                           cudaStream_t s);
 int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B, float *w2s,
-                     cudaStream_t s) {
-    if (w2s && conv2_tc_enabled(B)) return launch_conv2_fwd_tc(in, w, b, out, idx, B, w2s, s);
+                     cudaStream_t s, float *wd_also = nullptr) {
+    if (w2s && conv2_tc_enabled(B)) return launch_conv2_fwd_tc(in, w, b, out, idx, B, w2s, s, wd_also);
     return launch_conv2_fwd_simt(in, w, b, out, idx, B, s);
 }
 int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
@@ -345,7 +351,7 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
 }
 int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const float *p2, const uint8_t *i2,
                      const float *p1, const float *w, int B, float *dp1, float *c2w_part, float *wd, const Plan &pl,
-                     cudaStream_t s) {
+                     cudaStream_t s, bool wd_ready = false) {
     static unsigned long long attr_mask = 0;
     cudaError_t ea = ensure_dynamic_smem(conv2_bwd_kernel, kConv2BwdSmemBytes, &attr_mask);
     if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_bwd)");
@@ -363,8 +369,9 @@ int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const fl
         static unsigned long long tc_mask = 0;
         ea = ensure_dynamic_smem(tc::conv2_dgrad_tc_kernel, tc::kDgSmemBytes, &tc_mask);
         if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_dgrad_tc)");
-        CHECK_PDL(launch_pdl(tc::conv2_dgrad_weight_split_kernel, dim3(4 * tc::kDgChunks), dim3(128), 0, s, w, wd),
-                  "conv2 dgrad weight split (hi/lo)", s);
+        if (!wd_ready)   // (the fused training step builds it together with the forward operand)
+            CHECK_PDL(launch_pdl(tc::conv2_dgrad_weight_split_kernel, dim3(4 * tc::kDgChunks), dim3(128), 0, s, w, wd),
+                      "conv2 dgrad weight split (hi/lo)", s);
         tc::Conv2DgradTcArgs t{};
         t.dp2 = dp2; t.p2 = p2; t.wd = wd; t.i2 = i2; t.dp1 = dp1; t.split_stride = split_stride; t.nsplit = nsplit; t.B = B;
         const int npairs = (B + 1) / 2;
@@ -448,12 +455,14 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     int rc;
     if (phase == 2) {
         if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B,
-                                   w.dp1, w.c2w_part, w.wd, pl, s)))
+                                   w.dp1, w.c2w_part, w.wd, pl, s, pl.c2_presplit)))
             return rc;
         return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
     }
     if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s))) return rc;
-    if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, w.w2s, s))) return rc;
+    if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, w.w2s, s,
+                               backward && pl.c2_presplit ? w.wd : nullptr)))
+        return rc;
     int nsplit = 0;
     if ((rc = launch_fc1_fwd(w.p2, P + kOffF1W, P + kOffF1B, w.h, w.fc1_part, B, pl, s, &nsplit))) return rc;
     HeadArgs a{};
@@ -471,7 +480,7 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
         return rc;
     if (phase == 1) return 0;
     if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B, w.dp1,
-                               w.c2w_part, w.wd, pl, s)))
+                               w.c2w_part, w.wd, pl, s, pl.c2_presplit)))
         return rc;
     return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
 }

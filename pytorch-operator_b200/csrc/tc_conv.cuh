@@ -60,9 +60,7 @@ __device__ __forceinline__ void split_tf32(const float (&v)[4], uint4 &hi, uint4
 // conv2.weight [50][20][5][5] -> w2s[N tile][offset ky*5+kx][chunk][hi|lo][oc % NT][ic % 4], the shared-memory image
 // of the stacked B operands (rows >= 50 are zero).  One CTA per kernel offset.
 template <int NT>
-__global__ void __launch_bounds__(256) conv2_weight_split_kernel(const float *__restrict__ w, float *__restrict__ w2s) {
-    pdl_wait();
-    const int o = blockIdx.x;
+__device__ __forceinline__ void conv2_weight_split_block(const float *__restrict__ w, float *__restrict__ w2s, int o) {
     for (int i = threadIdx.x; i < (64 / NT) * kWnChunks * NT; i += blockDim.x) {
         const int tile = i / (kWnChunks * NT), rem = i - tile * (kWnChunks * NT), chunk = rem / NT, ol = rem - chunk * NT;
         const int oc = tile * NT + ol;
@@ -75,6 +73,11 @@ __global__ void __launch_bounds__(256) conv2_weight_split_kernel(const float *__
         *reinterpret_cast<uint4 *>(dst) = hi;
         *reinterpret_cast<uint4 *>(dst + NT * 4) = lo;
     }
+}
+template <int NT>
+__global__ void __launch_bounds__(256) conv2_weight_split_kernel(const float *__restrict__ w, float *__restrict__ w2s) {
+    pdl_wait();
+    conv2_weight_split_block<NT>(w, w2s, blockIdx.x);
 }
 
 template <int NT>

@@ -67,9 +67,9 @@ constexpr int kDcGroups = kP2Elems / 4;   // 200 per image
 
 // conv2.weight [50][500] -> wd[N tile t][chunk c][hi rows 0..127 | lo rows 128..255][oc % 4]: row n of tile t is
 // column t*125 + n of the [oc][(ic,ky,kx)] matrix (n >= 125 and oc >= 50 are zero).  One CTA per (tile, chunk).
-__global__ void __launch_bounds__(128) conv2_dgrad_weight_split_kernel(const float *__restrict__ w, float *__restrict__ wd) {
-    pdl_wait();
-    const int t = blockIdx.x / kDgChunks, c = blockIdx.x - t * kDgChunks, n = threadIdx.x;
+__device__ __forceinline__ void conv2_dgrad_weight_split_block(const float *__restrict__ w, float *__restrict__ wd, int blk) {
+    const int t = blk / kDgChunks, c = blk - t * kDgChunks, n = threadIdx.x;
+    if (n >= 128) return;
     float v[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
@@ -81,6 +81,18 @@ __global__ void __launch_bounds__(128) conv2_dgrad_weight_split_kernel(const flo
     float *dst = wd + (size_t)t * (kDgWBytes / 4) + (size_t)c * (kDgWPlane / 4) + n * 4;
     *reinterpret_cast<uint4 *>(dst) = hi;
     *reinterpret_cast<uint4 *>(dst + 128 * 4) = lo;
+}
+__global__ void __launch_bounds__(128) conv2_dgrad_weight_split_kernel(const float *__restrict__ w, float *__restrict__ wd) {
+    pdl_wait();
+    conv2_dgrad_weight_split_block(w, wd, blockIdx.x);
+}
+// Both operand copies of conv2.weight in one launch (training step: the weights do not change between the forward
+// and the backward pass): CTAs [0, 25) build the forward taps, the other 4 x kDgChunks the data-gradient tiles.
+__global__ void __launch_bounds__(256) conv2_weight_split_both_kernel(const float *__restrict__ w, float *__restrict__ w2s,
+                                                                      float *__restrict__ wd) {
+    pdl_wait();
+    if (blockIdx.x < 25) conv2_weight_split_block<32>(w, w2s, blockIdx.x);
+    else conv2_dgrad_weight_split_block(w, wd, blockIdx.x - 25);
 }
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
