@@ -86,14 +86,16 @@ def pool_tie_gap(params, x) -> float:
     return min(gaps)
 
 
-def relu_kink_gap(params, x) -> float:
-    """Smallest |pre-ReLU value| of any pooled conv2 output (float64): how close the batch comes to a ReLU kink of
-    mnist.py:28-29.  A pooled maximum within rounding of zero is switched on or off by the summation order (or, for
-    the 3xTF32 tensor-core convolution, by its ~1e-6 relative error), and that element's gradient with it."""
+def relu_kink_gap(params, x):
+    """(smallest |pre-ReLU value| of any pooled conv2 output, smallest |pre-ReLU value| of any fc1 output), float64:
+    how close the batch comes to a ReLU kink of mnist.py:28-31.  A value within rounding of zero is switched on or off
+    by the summation order (or, for the 3xTF32 tensor-core kernels, by their ~1e-6 relative error), and that element's
+    gradient with it."""
     pp = {k: v.double() for k, v in params.items()}
     a = F.max_pool2d(F.relu(F.conv2d(x.double(), pp["conv1.weight"], pp["conv1.bias"])), 2, 2)
-    pre = F.max_pool2d(F.conv2d(a, pp["conv2.weight"], pp["conv2.bias"]), 2, 2)
-    return float(pre.abs().min())
+    pre2 = F.max_pool2d(F.conv2d(a, pp["conv2.weight"], pp["conv2.bias"]), 2, 2)
+    z1 = F.linear(F.relu(pre2).reshape(-1, 800), pp["fc1.weight"], pp["fc1.bias"])
+    return float(pre2.abs().min()), float(z1.abs().min())
 
 
 def pool_choice_slack(params, x, idx1, idx2) -> float:

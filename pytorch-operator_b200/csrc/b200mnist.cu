@@ -237,10 +237,16 @@ int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *
 // sweep_tc_threshold.sh): B=128 96.3 / 94.2 us, B=256 163 / 134 us, B=512 294 / 223 us, B=4096 1.65 / 1.05 ms; at the
 // reference batch (64) they lose (their fixed costs -- TMEM allocation, zero-filled operand planes, 60-130 KB of weights
 // per CTA -- exceed the whole FFMA2 kernel).  So the conv kernels switch on at kTcConvMinBatch; the fc1 GEMMs need
-// M = B large enough to fill 128-row tiles on 148 SMs and switch at kTcMinBatch.
+// M = B large enough to fill 128-row tiles and switch at kTcMinBatch (tools/sweep_fc1_tc.sh, step time SIMT / tcgen05
+// fc1: B=256 131 / 137 us, B=384 178 / 165 us, B=512 213 / 182 us, B=768 295 / 239 us).
 // B200MNIST_CONV2_TC / _DGRAD_TC / _WGRAD_TC = 1 / 0 force each conv kernel on / off (tests, profiling).
-constexpr int kTcMinBatch = 1024;
+constexpr int kTcMinBatch = 384;
 constexpr int kTcConvMinBatch = 256;
+int fc1_tc_min_batch() {   // B200MNIST_FC1_TC_MIN overrides kTcMinBatch (threshold sweeps)
+    const char *e = getenv("B200MNIST_FC1_TC_MIN");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : kTcMinBatch;
+}
 bool tc_path_enabled(const char *env, int B) {   // read at every (uncaptured) launch: a few hundred ns, lets tests toggle it
     const char *e = getenv(env);
     return (!e || !e[0]) ? B >= kTcConvMinBatch : e[0] == '1';
@@ -301,7 +307,7 @@ int launch_fc1_bwd_tc(const float *dz1, const float *p2, const float *w1, float 
 // fc1 forward: returns the number of split-K partials left in `part` (0 = `h` is final).
 int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h, float *part, int B, const Plan &pl,
                    cudaStream_t s, int *nsplit_out) {
-    if (B >= kTcMinBatch) {
+    if (B >= fc1_tc_min_batch()) {
         *nsplit_out = 0;
         return launch_fc1_fwd_tc(in, w, bias, h, B, s);
     }
@@ -324,7 +330,7 @@ int launch_head(const HeadArgs &a, cudaStream_t s) {
 }
 int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
                   float *gw1, float *gb1, float *dp2_part, float *fc2w_part, const Plan &pl, cudaStream_t s) {
-    const bool use_tc = B >= kTcMinBatch && pl.dg_split == 1;  // large batch: both fc1 GEMMs on the tensor cores
+    const bool use_tc = B >= fc1_tc_min_batch() && pl.dg_split == 1;  // large batch: both fc1 GEMMs on the tensor cores
     FcBwdArgs a{};
     GemmArgs &g = a.wg;  // gW1[n,k] = sum_b dz1[b,n] p2[b,k] ; gb1[n] = sum_b dz1[b,n]
     g.A = dz1; g.B = p2; g.C = gw1; g.rowsum = gb1;

@@ -58,14 +58,15 @@ def tie_free_batch(params, B, seed, min_gap=5e-7):
     raise AssertionError("no tie-free batch found")
 
 
-def kink_free_batch(params, B, seed, min_abs=5e-6):
-    """synthetic_batch(B, seed'), with seed' the first seed >= `seed` whose pooled conv2 pre-activations all stay
-    `min_abs` away from zero (oracle.mnist_oracle.relu_kink_gap): the batches on which the 3xTF32 convolution and an
-    fp32 one must agree on every ReLU mask."""
+def kink_free_batch(params, B, seed, min_conv2=5e-6, min_fc1=0.0):
+    """synthetic_batch(B, seed'), with seed' the first seed >= `seed` whose pooled conv2 (and, if asked, fc1)
+    pre-activations all stay that far away from zero (oracle.mnist_oracle.relu_kink_gap): the batches on which the
+    3xTF32 kernels and fp32 ones must agree on every ReLU mask."""
     from oracle import mnist_oracle as mo
-    for s in range(seed, seed + 200):
+    for s in range(seed, seed + 400):
         x, t = mo.synthetic_batch(B, s)
-        if mo.relu_kink_gap(params, x) >= min_abs:
+        g2, g1 = mo.relu_kink_gap(params, x)
+        if g2 >= min_conv2 and g1 >= min_fc1:
             return x, t
     raise AssertionError("no kink-free batch found")
 

@@ -99,7 +99,8 @@ def _gpu_pool_indices(params, x):
     return i1.cpu(), i2.cpu()
 
 
-@pytest.mark.parametrize("B", [1, 2, 5, 63, 64, 65, 200, 300])  # 300: conv2 on tcgen05, fc1 on the SIMT GEMMs
+# 300: conv2 on tcgen05, fc1 on the SIMT GEMMs; 400: fc1 on tcgen05 as well
+@pytest.mark.parametrize("B", [1, 2, 5, 63, 64, 65, 200, 300, 400])
 def test_forward_backward_matches_oracles(B):
     """Loss, log-probs and all eight gradients of the fused forward+backward.
     (a) On ARBITRARY batches (near-ties in max-pool windows included) against the C oracle
@@ -110,7 +111,10 @@ def test_forward_backward_matches_oracles(B):
     pn = {k: v.numpy() for k, v in params.items()}
     net = _net()
     # (a)  (from TC_CONV_MIN_BATCH on: a batch whose conv2 ReLU masks are out of reach of the 3xTF32 error)
-    x, t = mo.synthetic_batch(B, 500 + B) if B < TC_CONV_MIN_BATCH else kink_free_batch(params, B, 500 + B)
+    if B < TC_CONV_MIN_BATCH:
+        x, t = mo.synthetic_batch(B, 500 + B)
+    else:   # fc1 joins the tensor-core path at 384 (kTcMinBatch): keep its ReLU masks out of reach as well
+        x, t = kink_free_batch(params, B, 500 + B, min_fc1=2e-6 if B >= 384 else 0.0)
     logp = torch.empty(B, 10, device=DEV)
     loss = float(net.forward_backward(x.to(DEV), t.to(DEV), logp_out=logp))
     got = _grads(net)
