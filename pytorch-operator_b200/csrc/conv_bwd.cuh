@@ -323,49 +323,63 @@ conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, c
                    const uint8_t *__restrict__ i1, float *__restrict__ part, int B) {
 
     pdl_wait();
+    // the image is staged as two column-parity planes, xs[c & 1][row][c >> 1]: lanes are consecutive windows, whose
+    // pixels are two columns apart -- in a plane they are neighbours, which halves the bank span of every load
+    // (ncu on the single-plane layout: 62 % of the shared-memory wavefronts were bank-conflict replays)
     __shared__ __align__(16) float xs[kXElems];
     const int tid = threadIdx.x, wid = tid >> 5, c = blockIdx.y * 10 + wid, lane = tid & 31;
     float acc[25], accb = 0.f;
 #pragma unroll
     for (int k = 0; k < 25; ++k) acc[k] = 0.f;
+    // per window: gradient and the plane offsets of the arg-max pixel for even kernel columns (oa) and odd ones (ob)
     float gl[5], gl_n[5];
-    int ol[5], ol_n[5];
+    int oa[5], ob[5], oa_n[5], ob_n[5];
     float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), xv_n = xv;
-    auto fetch = [&](int b, float (&g)[5], int (&o)[5], float4 &xq) {
+    auto fetch = [&](int b, float (&g)[5], int (&pa)[5], int (&pb)[5], float4 &xq) {
         const size_t base = ((size_t)b * 20 + c) * 144;
         if (tid < kXElems / 4) xq = __ldg(reinterpret_cast<const float4 *>(x + (size_t)b * kXElems) + tid);
 #pragma unroll
         for (int j = 0; j < 5; ++j) {
             const int wl = j * 32 + lane;
             g[j] = 0.f;
-            o[j] = 0;
+            pa[j] = 0;
+            pb[j] = 0;
             if (wl < 144) {
                 const float pv = __ldcg(p1 + base + wl);
                 const float gv = __ldcg(dp1 + base + wl);
                 const int q = i1[base + wl];
                 g[j] = pv > 0.f ? gv : 0.f;
-                o[j] = (2 * (wl / 12) + (q >> 1)) * 28 + 2 * (wl % 12) + (q & 1);
+                const int dx = q & 1, at = (2 * (wl / 12) + (q >> 1)) * 14 + wl % 12;   // pixel column 2 wx + dx
+                pa[j] = dx * 392 + at;               // column 2 wx + dx + kx, kx even: plane dx, offset + kx / 2
+                pb[j] = (dx ^ 1) * 392 + at + dx;    // kx odd: the other plane, offset + (kx - 1) / 2 (+ 1 if dx)
             }
         }
     };
-    if ((int)blockIdx.x < B) fetch(blockIdx.x, gl_n, ol_n, xv_n);
+    if ((int)blockIdx.x < B) fetch(blockIdx.x, gl_n, oa_n, ob_n, xv_n);
     for (int b = blockIdx.x; b < B; b += gridDim.x) {
 #pragma unroll
-        for (int j = 0; j < 5; ++j) { gl[j] = gl_n[j]; ol[j] = ol_n[j]; }
+        for (int j = 0; j < 5; ++j) { gl[j] = gl_n[j]; oa[j] = oa_n[j]; ob[j] = ob_n[j]; }
         xv = xv_n;
-        if (b + (int)gridDim.x < B) fetch(b + gridDim.x, gl_n, ol_n, xv_n);
+        if (b + (int)gridDim.x < B) fetch(b + gridDim.x, gl_n, oa_n, ob_n, xv_n);
         __syncthreads();  // previous image's readers of xs are done
-        if (tid < kXElems / 4) reinterpret_cast<float4 *>(xs)[tid] = xv;
+        if (tid < kXElems / 4) {   // pixels 4 tid .. 4 tid + 3 of one row: columns col, col + 2 -> plane 0; col + 1, col + 3 -> plane 1
+            const int row = tid / 7, half = (tid - row * 7) * 2;
+            *reinterpret_cast<float2 *>(&xs[row * 14 + half]) = make_float2(xv.x, xv.z);
+            *reinterpret_cast<float2 *>(&xs[392 + row * 14 + half]) = make_float2(xv.y, xv.w);
+        }
         __syncthreads();
 #pragma unroll
         for (int j = 0; j < 5; ++j) {
             const float g = gl[j];
-            const float *px = xs + ol[j];
+            const float *pe = xs + oa[j], *po = xs + ob[j];
             accb += g;
 #pragma unroll
             for (int ky = 0; ky < 5; ++ky)
 #pragma unroll
-                for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] = fmaf(g, px[ky * 28 + kx], acc[ky * 5 + kx]);
+                for (int kx = 0; kx < 5; ++kx) {
+                    const float v = (kx & 1) ? po[ky * 14 + (kx - 1) / 2] : pe[ky * 14 + kx / 2];
+                    acc[ky * 5 + kx] = fmaf(g, v, acc[ky * 5 + kx]);
+                }
         }
     }
     float mine = 0.f;   // lane k < 25 ends up with tap k, lane 25 with the bias gradient
