@@ -100,3 +100,23 @@ def test_smoke_sendrecv_bit_exact():
     for w, res in enumerate(mo.smoke_sendrecv(inp, 3), start=1):
         assert np.array_equal(res.numpy(), gold[f"result_from_worker{w}"])
         assert np.array_equal(c_oracle.square(inp.numpy()), gold[f"result_from_worker{w}"])
+
+
+def test_kink_and_tie_gaps_select_usable_batches():
+    """The batch selectors the GPU parity tests rely on: pool_tie_gap / relu_kink_gap are positive distances, a batch
+    returned by tie_free_batch / kink_free_batch honours the bound, and the gaps react to a planted near-tie."""
+    from tests.helpers import kink_free_batch, tie_free_batch
+    params = mo.init_params(1)
+    x, _ = tie_free_batch(params, 4, 100, min_gap=5e-7)
+    assert mo.pool_tie_gap(params, x) >= 5e-7
+    x, _ = kink_free_batch(params, 8, 200, min_conv2=5e-6, min_fc1=2e-6)
+    g2, g1 = mo.relu_kink_gap(params, x)
+    assert g2 >= 5e-6 and g1 >= 2e-6
+    # a bias that puts one pooled conv2 pre-activation exactly on the kink drives the conv2 gap to ~0
+    pp = {k: v.clone() for k, v in params.items()}
+    a = torch.nn.functional.max_pool2d(torch.relu(torch.nn.functional.conv2d(x.double(), pp["conv1.weight"].double(),
+                                                                             pp["conv1.bias"].double())), 2, 2)
+    pre = torch.nn.functional.max_pool2d(torch.nn.functional.conv2d(a, pp["conv2.weight"].double(),
+                                                                    pp["conv2.bias"].double()), 2, 2)
+    pp["conv2.bias"][0] -= pre[0, 0, 0, 0].float()
+    assert mo.relu_kink_gap(pp, x)[0] < 1e-6
