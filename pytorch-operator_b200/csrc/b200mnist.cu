@@ -234,14 +234,14 @@ int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *
     return 0;
 }
 // Which conv2 kernels run inside the fused step.  Measured step time, tcgen05 conv kernels off / on (tools/
-// sweep_tc_threshold.sh): B=128 96.3 / 94.2 us, B=256 163 / 134 us, B=512 294 / 223 us, B=4096 1.65 / 1.05 ms; at the
+// sweep_tc_threshold.sh): B=96 84.3 / 88.0 us, B=128 94.3 / 90.2 us, B=192 129 / 115 us, B=256 163 / 134 us, B=512 294 / 223 us; at the
 // reference batch (64) they lose (their fixed costs -- TMEM allocation, zero-filled operand planes, 60-130 KB of weights
 // per CTA -- exceed the whole FFMA2 kernel).  So the conv kernels switch on at kTcConvMinBatch; the fc1 GEMMs need
 // M = B large enough to fill 128-row tiles and switch at kTcMinBatch (tools/sweep_fc1_tc.sh, step time SIMT / tcgen05
 // fc1: B=256 131 / 137 us, B=384 178 / 165 us, B=512 213 / 182 us, B=768 295 / 239 us).
 // B200MNIST_CONV2_TC / _DGRAD_TC / _WGRAD_TC = 1 / 0 force each conv kernel on / off (tests, profiling).
 constexpr int kTcMinBatch = 384;
-constexpr int kTcConvMinBatch = 256;
+constexpr int kTcConvMinBatch = 128;
 int fc1_tc_min_batch() {   // B200MNIST_FC1_TC_MIN overrides kTcMinBatch (threshold sweeps)
     const char *e = getenv("B200MNIST_FC1_TC_MIN");
     const int v = e ? atoi(e) : 0;

@@ -74,7 +74,7 @@ def test_forward_layers_match_c_oracle(B):
     assert_close(h.cpu().numpy(), act["h"], what="h")
 
 
-TC_CONV_MIN_BATCH = 256   # mirrors kTcConvMinBatch in csrc/b200mnist.cu
+TC_CONV_MIN_BATCH = 128   # mirrors kTcConvMinBatch in csrc/b200mnist.cu
 
 
 def _gpu_pool_indices(params, x):
@@ -99,7 +99,7 @@ def _gpu_pool_indices(params, x):
     return i1.cpu(), i2.cpu()
 
 
-# 300: conv2 on tcgen05, fc1 on the SIMT GEMMs; 400: fc1 on tcgen05 as well
+# 200, 300: conv2 on tcgen05, fc1 on the SIMT GEMMs; 400: fc1 on tcgen05 as well
 @pytest.mark.parametrize("B", [1, 2, 5, 63, 64, 65, 200, 300, 400])
 def test_forward_backward_matches_oracles(B):
     """Loss, log-probs and all eight gradients of the fused forward+backward.
