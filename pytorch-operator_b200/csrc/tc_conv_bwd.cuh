@@ -342,7 +342,8 @@ constexpr int kWgAPlane = 128 * 16;        // 4 positions x 128 rows
 constexpr int kWgABytes = 16 * kWgAPlane;  // 64 positions: 32,768 B
 constexpr int kWgBChunk = 48 * 16;         // 4 positions x 48 rows (one input row y)
 constexpr int kWgBBytes = 2 * 12 * kWgBChunk;   // 2 chunks x 12 input rows: 18,432 B
-constexpr int kWgAccFloats = 5 * 20 * 64 + 64;  // [ky][ic][oc] + bias[oc]
+constexpr int kWgAccLd = 65;                    // floats per (ky, ic) row of the fp32 sums: 64 oc + 1 (conflict-free both ways)
+constexpr int kWgAccFloats = 5 * 20 * kWgAccLd + 64 + 4;  // [ky][ic][oc] + bias[oc] (8-byte multiple for the barriers behind it)
 constexpr int kWgSmemBytes = 2 * (kWgABytes + kWgBBytes) + 2 * kWgAccFloats * 4 + 256 + 128;
 
 struct Conv2WgradTcArgs {
@@ -521,19 +522,19 @@ __global__ void __launch_bounds__(kWgThreads, 1) conv2_wgrad_tc_kernel(const Con
 #pragma unroll
                 for (int ic = 0; ic < 20; ++ic) {     // x p1_hi (n = ic) + x p1_lo (n = 24 + ic)
                     const float lo = __uint_as_float(24 + ic < 32 ? r[24 + ic] : r2[24 + ic - 32]);
-                    mine[(ky * 20 + ic) * 64] += __uint_as_float(r[ic]) + lo;
+                    mine[(ky * 20 + ic) * kWgAccLd] += __uint_as_float(r[ic]) + lo;
                 }
-                if (ky == 0) mine[5 * 20 * 64] += __uint_as_float(r[20]);   // ones row: bias gradient
+                if (ky == 0) mine[5 * 20 * kWgAccLd] += __uint_as_float(r[20]);   // ones row: bias gradient
             }
         }
         asm volatile("bar.sync 2, 128;" ::: "memory");
         float *po = g.part + (size_t)slice * kC2PartStride;
-        for (int i = row; i < 5 * 20 * 50; i += 128) {        // (ky, ic, oc), oc fastest; hi rows + lo rows
-            const int o = i % 50, r = i / 50, ic = r % 20, ky = r / 20;
-            const int si = (ky * 20 + ic) * 64 + o;
-            po[o * 500 + ic * 25 + ky * 5 + kx] = acc_s[si] + acc_s[kWgAccFloats + si];
+        for (int i = row; i < 5 * 20 * 50; i += 128) {        // (oc, ic, ky), ky fastest: consecutive threads write 20 bytes apart
+            const int o = i / 100, r = i - o * 100, ic = r / 5, ky = r - ic * 5;
+            const int si = (ky * 20 + ic) * kWgAccLd + o;
+            po[o * 500 + ic * 25 + ky * 5 + kx] = acc_s[si] + acc_s[kWgAccFloats + si];   // hi rows + lo rows
         }
-        if (kx == 0 && row < 50) po[25024 + row] = acc_s[5 * 20 * 64 + row] + acc_s[kWgAccFloats + 5 * 20 * 64 + row];
+        if (kx == 0 && row < 50) po[25024 + row] = acc_s[5 * 20 * kWgAccLd + row] + acc_s[kWgAccFloats + 5 * 20 * kWgAccLd + row];
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
