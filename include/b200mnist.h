@@ -173,7 +173,10 @@ int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const f
                      float *gw2, float *gb2, float *gw1, float *gb1, float *dp2, void *scratch, void *stream);
 /* Backward of conv2+ReLU+pool, mnist.py:42: given dp2 [B,50,4,4] (gradient of the pooled
  * output), the saved p2/idx2/p1 and conv2.weight, writes gw [50,20,5,5], gb [50] and
- * dp1 [B,20,12,12].  scratch: b200mnist_conv2_bwd_scratch_bytes(B). */
+ * dp1 [B,20,12,12].  scratch: b200mnist_conv2_bwd_scratch_bytes(B).  dp2, p2, p1, w and scratch must be
+ * 16-byte aligned, idx2 4-byte aligned (vector loads).  From B >= 128 the data and the weight gradient run on the
+ * tensor cores (tcgen05, 3xTF32); B200MNIST_CONV2_DGRAD_TC / B200MNIST_CONV2_WGRAD_TC = 1 / 0 in the environment
+ * force either kernel on / off. */
 int64_t b200mnist_conv2_bwd_scratch_bytes(int B);
 int b200mnist_conv2_bwd(const float *dp2, const float *p2, const uint8_t *idx2, const float *p1, const float *w,
                         int B, float *gw, float *gb, float *dp1, void *scratch, void *stream);
