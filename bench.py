@@ -160,21 +160,16 @@ def cpu_reference_run(batch, steps, warmup, budget_s, threads=None):
             "ms_per_step": 1e3 * dt / done, "steps": done}
 
 
-def cpu_reference_run_ddp(batch, steps, warmup, budget_s, world):
-    """The reference's CPU/gloo configuration (BASELINE configs[0] generalised to `world` ranks): `world` local
-    processes, DistributedDataParallel on gloo, host cores split evenly between the ranks."""
-    import tempfile
-
+def cpu_reference_run_ddp(batch, steps, warmup, budget_s, world, hard_timeout_s=150.0):
+    """The reference's CPU/gloo configuration (BASELINE configs[0] generalised to `world` ranks): `world` fresh
+    local processes, DistributedDataParallel on gloo, host cores split evenly between the ranks.  The processes get
+    a clean environment and their own tcp:// store (oracle.mnist_oracle.run_ddp_cpu), and are killed after
+    `hard_timeout_s`, so this arm also works -- and stays bounded -- when bench.py itself runs under torchrun."""
     import torch
-    import torch.multiprocessing as mp
     from oracle import mnist_oracle as mo
     cores = os.cpu_count() or 1
     threads = max(1, cores // world)
-    path = os.path.join(tempfile.mkdtemp(), "ddp_cpu.json")
-    port = 29700 + (os.getpid() % 200)
-    mp.spawn(mo.ddp_cpu_worker, args=(world, port, batch, steps, warmup, budget_s, threads, path), nprocs=world, join=True)
-    with open(path) as f:
-        r = json.load(f)
+    r = mo.run_ddp_cpu(world, batch, steps, warmup, budget_s, threads, hard_timeout_s)
     return {"value": r["value"], "unit": UNIT, "cores": threads * world, "kind": "port",
             "sample": f"{r['steps']} DDP training steps, {world} gloo ranks x batch {batch} x {threads} threads "
                       f"(reference train() body + DistributedDataParallel on torch {torch.__version__} CPU ops, "
@@ -182,21 +177,36 @@ def cpu_reference_run_ddp(batch, steps, warmup, budget_s, world):
             "ms_per_step": r["ms_per_step"], "steps": r["steps"]}
 
 
+REFERENCE_MIN_STEPS = 200   # a 20-step CPU sample swings by +-15 %; the arm is time-budgeted instead
+
+
 def run_reference_arm(args, rank):
+    """bench.py --impl reference: the reference's own CPU implementation of the step (torch CPU ops, autograd,
+    optim.SGD, gloo DistributedDataParallel at N>1) on the box's host cores.  Under torchrun only rank 0 works; the
+    other ranks return at once (exit 0)."""
     if rank != 0:
         return
+    steps = max(args.steps, REFERENCE_MIN_STEPS)
+    warmup = max(args.warmup, 3)
+    note = ""
+    r = None
     if args.gpus > 1:
-        r = cpu_reference_run_ddp(args.batch, args.steps, max(args.warmup, 3), budget_s=120.0, world=args.gpus)
-        how = f"reference CPU path: {args.gpus} gloo ranks with DistributedDataParallel, per-rank batch {args.batch}"
-    else:
-        r = cpu_reference_run(args.batch, args.steps, max(args.warmup, 3), budget_s=150.0)
+        try:
+            r = cpu_reference_run_ddp(args.batch, steps, warmup, budget_s=args.ref_budget, world=args.gpus)
+            how = f"reference CPU path: {args.gpus} gloo ranks with DistributedDataParallel, per-rank batch {args.batch}"
+        except Exception as e:   # bounded by the watchdog; fall back to the single-process arm rather than no number
+            note = f"; gloo DDP arm failed ({e!r}), single-process CPU run reported instead"
+    if r is None:
+        import torch
+        torch.set_num_threads(os.cpu_count() or 1)   # torchrun exports OMP_NUM_THREADS=1 to its workers
+        r = cpu_reference_run(args.batch, steps, warmup, budget_s=args.ref_budget)
         how = "reference CPU path, single process"
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
-            "steps": r["steps"], "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"],
+            "steps": r["steps"], "warmup": warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"examples/mnist Net DDP train step (BASELINE configs[{1 if args.gpus == 1 else 2}]), "
                                    f"per-rank batch {args.batch}, synthetic 1x28x28", "global_batch": args.gpus * args.batch,
-                       "how": how + "; steps capped by a time budget"},
+                       "how": how + f"; at least {REFERENCE_MIN_STEPS} timed steps, capped by a {args.ref_budget:g} s budget" + note},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -211,6 +221,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64, help="per-rank batch (BASELINE configs[1]: 64; config 5: 4096)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-budget", type=float, default=20.0, help="--impl reference: seconds of timed CPU work")
     ap.add_argument("--profile-iters", type=int, default=30)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))

@@ -235,15 +235,19 @@ class OracleNet(torch.nn.Module):
 def ddp_cpu_worker(rank, world, port, batch, steps, warmup, budget_s, threads, result_path):
     """One rank of the reference's CPU/gloo configuration (BASELINE.json configs[0]; mnist.py:116,136-140):
     DistributedDataParallel on gloo, optim.SGD(lr=.01, momentum=.5), per-rank synthetic batches.  Rank 0
-    writes {value: global images/s, ...} as JSON to result_path."""
+    writes {value: global images/s, ...} as JSON to result_path.
+
+    Rendezvous is an explicit ``tcp://127.0.0.1:<port>`` store hosted by rank 0 of THIS group: the caller may
+    itself be a torchrun worker, whose TORCHELASTIC_* / MASTER_* variables would otherwise point ``env://`` at
+    the elastic agent's store, where nobody serves this group (the round-1 hang)."""
+    import datetime
     import json
-    import os
     import time
 
     import torch.distributed as dist
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     torch.set_num_threads(max(1, threads))
-    dist.init_process_group("gloo")
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                            timeout=datetime.timedelta(seconds=60))
     torch.manual_seed(1)
     model = torch.nn.parallel.DistributedDataParallel(OracleNet())
     opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.5)
@@ -274,3 +278,68 @@ def ddp_cpu_worker(rank, world, port, batch, steps, warmup, budget_s, threads, r
             json.dump({"value": world * batch * n / dt, "steps": n, "ms_per_step": 1e3 * dt / n, "seconds": dt,
                        "threads_per_rank": max(1, threads), "world": world}, f)
     dist.destroy_process_group()
+
+
+# environment a torchrun / launcher parent leaves behind that must not leak into the CPU baseline's own group
+_SCRUB_PREFIXES = ("TORCHELASTIC_", "TORCH_NCCL_", "NCCL_", "PET_")
+_SCRUB_NAMES = ("MASTER_ADDR", "MASTER_PORT", "RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK",
+                "GROUP_WORLD_SIZE", "ROLE_RANK", "ROLE_WORLD_SIZE", "ROLE_NAME", "OMP_NUM_THREADS",
+                "CUDA_VISIBLE_DEVICES")
+
+
+def clean_env(env=None):
+    """A copy of ``env`` (default os.environ) without any rendezvous / elastic-agent variable."""
+    import os
+    env = dict(os.environ if env is None else env)
+    for k in list(env):
+        if k in _SCRUB_NAMES or k.startswith(_SCRUB_PREFIXES):
+            del env[k]
+    return env
+
+
+def run_ddp_cpu(world, batch, steps, warmup, budget_s, threads, hard_timeout_s):
+    """Start ``world`` fresh interpreter processes (clean environment, own tcp store on a free port) running
+    ``ddp_cpu_worker`` and return rank 0's result dict.  Every child is killed when ``hard_timeout_s`` expires:
+    this arm can cost the caller at most that long, whatever goes wrong inside it."""
+    import json
+    import os
+    import socket
+    import subprocess
+    import sys
+    import tempfile
+    import time
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    path = os.path.join(tempfile.mkdtemp(), "ddp_cpu.json")
+    env = clean_env()
+    env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
+    env["CUDA_VISIBLE_DEVICES"] = ""  # the CPU arm must not touch (or initialise) a GPU
+    procs = [subprocess.Popen([sys.executable, "-m", "oracle.mnist_oracle", "ddp-worker", str(r), str(world), str(port),
+                               str(batch), str(steps), str(warmup), str(budget_s), str(threads), path],
+                              env=env, cwd=root) for r in range(world)]
+    deadline = time.monotonic() + hard_timeout_s
+    rcs = []
+    for p in procs:
+        try:
+            rcs.append(p.wait(timeout=max(0.1, deadline - time.monotonic())))
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                if q.poll() is None:
+                    q.kill()
+            raise TimeoutError(f"gloo DDP CPU baseline did not finish within {hard_timeout_s:.0f} s") from None
+    if any(rcs):
+        raise RuntimeError(f"gloo DDP CPU baseline: worker exit codes {rcs}")
+    with open(path) as f:
+        return json.load(f)
+
+
+if __name__ == "__main__":
+    import sys
+    if len(sys.argv) >= 11 and sys.argv[1] == "ddp-worker":
+        a = sys.argv[2:]
+        ddp_cpu_worker(int(a[0]), int(a[1]), int(a[2]), int(a[3]), int(a[4]), int(a[5]), float(a[6]), int(a[7]), a[8])
+    else:
+        raise SystemExit("usage: python -m oracle.mnist_oracle ddp-worker RANK WORLD PORT BATCH STEPS WARMUP BUDGET_S "
+                         "THREADS RESULT_PATH")

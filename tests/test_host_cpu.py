@@ -2,6 +2,7 @@
 header declares, host-side argument validation, the operator env contract, the payload CLI,
 and the world_size-2 host logic of the flat-bucket DDP on gloo.  No kernel is launched here."""
 import ctypes
+import json
 import os
 import re
 import subprocess
@@ -160,3 +161,23 @@ def test_flat_bucket_ddp_host_logic_world_size_2_gloo():
     for rank, ok_bcast, ok_sum, ok_views, scale, first_key in res:
         assert ok_bcast and ok_sum and ok_views, (rank, ok_bcast, ok_sum, ok_views)
         assert scale == 0.5 and first_key == "module.conv1.weight"
+
+
+def test_reference_arm_survives_a_torchrun_environment():
+    """bench.py --impl reference at N>1 must not inherit the elastic agent's rendezvous (round 1: the gloo
+    children connected to the agent's store and the arm hung for 812 s): run it with the variables torchrun
+    exports to a worker, pointing at a port where nobody listens."""
+    env = dict(os.environ, PYTHONPATH=ROOT, TORCHELASTIC_USE_AGENT_STORE="True", TORCHELASTIC_RUN_ID="x",
+               MASTER_ADDR="127.0.0.1", MASTER_PORT="1", RANK="0", WORLD_SIZE="2", LOCAL_RANK="0",
+               GROUP_RANK="0", OMP_NUM_THREADS="1")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
+                        "--steps", "3", "--warmup", "3", "--ref-budget", "1"], env=env, capture_output=True, text=True,
+                       timeout=240)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
+    assert "2 gloo ranks" in line["cpu_baseline"]["sample"] and "failed" not in line["config"]["how"]
+    # every other rank of the torchrun group exits 0 without work and without output
+    r1 = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
+                        env=dict(env, RANK="1", LOCAL_RANK="1"), capture_output=True, text=True, timeout=60)
+    assert r1.returncode == 0 and r1.stdout.strip() == ""
