@@ -126,7 +126,8 @@ int b200mnist_conv2_relu_pool_fwd(const float *in, const float *w, const float *
  * pair is staged once in shared memory; each of the 25 kernel offsets is an MMA whose operand descriptor points at
  * the same planes shifted by (ky,kx)), tcgen05.mma kind::tf32 with the 3xTF32 split, pooling in the epilogue.
  * `scratch` (b200mnist_conv2_fwd_tc_scratch_bytes() bytes, 16-byte aligned) receives the hi/lo-split weights.
- * The fused step uses this path when B200MNIST_CONV2_TC=1 is set in the environment. */
+ * b200mnist_conv2_relu_pool_fwd and the fused step take this path from B >= 128 (measured break-even);
+ * B200MNIST_CONV2_TC = 1 / 0 in the environment forces it on / off. */
 int64_t b200mnist_conv2_fwd_tc_scratch_bytes(void);
 int b200mnist_conv2_relu_pool_fwd_tc(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
                                      int B, void *scratch, void *stream);
@@ -137,7 +138,8 @@ int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, f
                            void *stream);
 /* The same F.relu(fc1(x)) (mnist.py:31) forced onto the tensor-core path: TMA-fed tcgen05.mma kind::tf32 with
  * the 3xTF32 error-compensated split (fp32-level accuracy), accumulator in TMEM.  b200mnist_fc1_relu_fwd and the
- * fused step pick it automatically for B >= 1024; this entry point exists so it can be tested at any B. */
+ * fused step pick it automatically for B >= 384 (B200MNIST_FC1_TC_MIN in the environment moves the threshold);
+ * this entry point exists so it can be tested at any B. */
 int b200mnist_fc1_relu_fwd_tc(const float *in, const float *w, const float *bias, float *out, int B, void *stream);
 /* F.log_softmax(fc2(h), dim=1) and F.nll_loss (mean), mnist.py:32-33,41, plus the start of
  * loss.backward() (mnist.py:42): dz2 = (softmax - onehot)/B and dz1 = (dz2 . W2) * (h > 0).
@@ -155,8 +157,12 @@ int b200mnist_fc2_logsoftmax_nll(const float *h, const float *w, const float *bi
  * that loads the library, for the life of the process), hence the limit
  * B <= B200MNIST_STATIC_MAX_BATCH; larger B returns -10006 with an explanatory message.
  * The call allocates nothing (no cudaMalloc/cudaFree, no allocating library routine).
- * The FIRST call on each device looks up the array's device address (a one-time, per-device
- * set-up that is not stream work): make that first call before starting any stream capture.
+ * The FIRST call on each device looks up the array's device address (a per-device set-up
+ * that is not stream work): make that first call before starting any stream capture.  The
+ * address is looked up again on every call made outside a capture; a call made while the stream
+ * is capturing uses the address remembered from the last such look-up on that device ordinal, so
+ * after cudaDeviceReset (or any re-creation of the device's context) make one uncaptured call
+ * before capturing again -- and a graph captured before the reset must not be replayed.
  * All calls on a device share the one array: two calls whose kernels may overlap on the GPU
  * (different streams, no ordering between them) race on it -- serialise them. */
 #define B200MNIST_STATIC_MAX_BATCH 4096

@@ -43,13 +43,16 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if os.path.exists(SO_PATH):
             return SO_PATH  # sources look newer (e.g. fresh checkout mtimes) but no compiler: use what travelled
         raise RuntimeError("libb200mnist.so is missing and nvcc is not available to build it")
-    cmd = [nvcc, *NVCC_FLAGS, "-o", SO_PATH + ".tmp", os.path.join(_SRC_DIR, "b200mnist.cu")]
+    tmp = f"{SO_PATH}.{os.getpid()}.tmp"  # per process: several ranks may find the library stale at the same time
+    cmd = [nvcc, *NVCC_FLAGS, "-o", tmp, os.path.join(_SRC_DIR, "b200mnist.cu")]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
+        if os.path.exists(tmp):
+            os.unlink(tmp)
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-    os.replace(SO_PATH + ".tmp", SO_PATH)
+    os.replace(tmp, SO_PATH)  # atomic: a concurrent loader sees the old or the new file, never a partial one
     if verbose:
         print(res.stderr)
     return SO_PATH

@@ -133,12 +133,12 @@ Plan make_plan(int B) {
         ov[0] = 0;
         if (const char *e = getenv("B200MNIST_PLAN")) sscanf(e, "%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3]);
     }
-    if (ov[0] > 0) {
-        p.fc1_kchunk = ceil_div(ceil_div(800, ov[0]), kGemmBK) * kGemmBK;
+    if (ov[0] > 0) {   // clamped to what the workspace regions and sum_partials<> are sized for
+        p.fc1_kchunk = ceil_div(ceil_div(800, clampi(ov[0], 1, 10)), kGemmBK) * kGemmBK;
         p.fc1_split = ceil_div(800, p.fc1_kchunk);
     }
     if (ov[1] > 0) {
-        p.dg_kchunk = ceil_div(ceil_div(500, ov[1]), kGemmBK) * kGemmBK;
+        p.dg_kchunk = ceil_div(ceil_div(500, clampi(ov[1], 1, 8)), kGemmBK) * kGemmBK;
         p.dg_split = ceil_div(500, p.dg_kchunk);
     }
     if (ov[2] > 0) p.c2w_split = clampi(ov[2], 1, 32);
@@ -700,16 +700,22 @@ int b200mnist_fc2_logsoftmax_nll_static(const float *h, const float *w, const fl
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
     if (dev < 0 || dev >= kMaxDevices) return fail_arg(7, "device ordinal out of range for the static scratch table");
-    if (!g_head_scratch_addr[dev]) {
-        // One-time set-up for this device, with this device current.  In host code the name
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    e = cudaStreamIsCapturing(s, &cap);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaStreamIsCapturing");
+    if (!g_head_scratch_addr[dev] || cap == cudaStreamCaptureStatusNone) {
+        // Set-up for this device, with this device current.  In host code the name
         // g_head_scratch is only a handle for the symbol, not an address a kernel can use:
-        // the real per-device address has to be asked for.
+        // the real per-device address has to be asked for.  The answer is remembered per
+        // device ordinal for calls made while the stream is being captured; outside a
+        // capture it is asked for again on every call (cheap), so an address remembered
+        // before a cudaDeviceReset / context re-creation is not trusted afterwards.
         void *p = nullptr;
         e = cudaGetSymbolAddress(&p, g_head_scratch);
         if (e != cudaSuccess) return fail_cuda(e, "cudaGetSymbolAddress(g_head_scratch)");
         g_head_scratch_addr[dev] = static_cast<float *>(p);
     }
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
     float *scratch = g_head_scratch_addr[dev];
     // The array keeps whatever the previous call left in it.  Only the ticket word at its head
     // has to start from zero (the per-row slots are fully rewritten before they are read).

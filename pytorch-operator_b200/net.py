@@ -335,6 +335,23 @@ class StepGraph:
         return self.loss
 
 
+class StepLoss:
+    """What ``StepPipeline.submit`` returns: the loss of the step just enqueued.  The step's last kernel stores it
+    in pinned host memory asynchronously, so reading it means waiting for THAT step -- ``item()`` (what
+    mnist.py:47 calls) and ``float()`` synchronise on the step's completion event first, like ``loss.item()`` on a
+    CUDA tensor does in the reference.  Read it before the same slot is submitted again (two steps later)."""
+    __slots__ = ("_pipe", "_slot")
+
+    def __init__(self, pipe, slot):
+        self._pipe, self._slot = pipe, slot
+
+    def item(self) -> float:
+        self._pipe.ev_done[self._slot].synchronize()
+        return float(self._pipe.loss_host[self._slot])
+
+    __float__ = item
+
+
 class StepPipeline:
     """Double-buffered host-fed training: while step i runs (graph replay on the current stream),
     the pinned host batch of step i+1 is copied to the other static input buffer on a copy stream;
@@ -342,7 +359,7 @@ class StepPipeline:
 
         pipe = StepPipeline(model, optimizer, batch)
         for rec in pinned_records:          # uint8 [batch*784*4 + batch*8]: fp32 images, then int64 targets
-            loss = pipe.submit(rec)         # asynchronous; a 0-d view of pinned host memory, valid after drain()
+            loss = pipe.submit(rec)         # asynchronous; loss.item() waits for that step only
         pipe.drain()                        # pipe.loss_host[k] holds the loss of the last step on slot k
     """
 
@@ -379,20 +396,20 @@ class StepPipeline:
                                                          self.copy_stream.cuda_stream, main.cuda_stream,
                                                          self.ev_done[k].cuda_event, self.ev_copied[k].cuda_event),
                         "stage_inputs")
-            loss = g.replay()
+            g.replay()
             _cabi.check(self._lib.b200mnist_event_record(self.ev_done[k].cuda_event, main.cuda_stream), "event_record")
             self.steps += 1
-            return loss
+            return StepLoss(self, k)
         if host_record.is_cuda:                             # already on the device (DeviceMNIST): plain D2D on the
             if target is None:                              # compute stream, ordered after whatever produced it
                 packed.copy_(host_record, non_blocking=True)
             else:
                 g.x.copy_(host_record, non_blocking=True)
                 g.target.copy_(target, non_blocking=True)
-            loss = g.replay()
+            g.replay()
             self.ev_done[k].record(main)
             self.steps += 1
-            return loss
+            return StepLoss(self, k)
         self.copy_stream.wait_event(self.ev_done[k])        # slot k's previous step has consumed its inputs
         with torch.cuda.stream(self.copy_stream):           # H2D of this step's inputs, off the compute stream
             if target is None:
@@ -402,10 +419,10 @@ class StepPipeline:
                 g.target.copy_(target, non_blocking=True)
             self.ev_copied[k].record(self.copy_stream)
         main.wait_event(self.ev_copied[k])
-        loss = g.replay()
+        g.replay()
         self.ev_done[k].record(main)
         self.steps += 1
-        return loss
+        return StepLoss(self, k)
 
     def drain(self):
         torch.cuda.current_stream().synchronize()

@@ -39,6 +39,25 @@ def test_payload_cli_runs_and_prints_reference_lines(tmp_path):
     assert abs(float(lines[0].split("loss=")[1]) - float(lo)) < 1e-4
 
 
+def test_payload_logged_losses_are_the_current_step(tmp_path):
+    """mnist.py:47 prints loss.item() of the step just run.  The pipelined (CUDA-graph) loop writes the loss
+    asynchronously into pinned host memory, so every 'loss=' line after batch 0 must wait for its own step:
+    the lines of a pipelined run equal those of an eager (--no-graph) run, batch for batch."""
+    env = dict(os.environ, PYTHONPATH=ROOT, WORLD_SIZE="1")
+    env.pop("RANK", None)
+    outs = []
+    for extra in ([], ["--no-graph"]):
+        r = subprocess.run([sys.executable, "-m", "pytorch_operator_b200.mnist", "--synthetic", "45", "--batch-size", "64",
+                            "--test-batch-size", "100", "--log-interval", "4", "--dir", str(tmp_path / "logs"), *extra],
+                           env=env, cwd=str(tmp_path), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append([ln for ln in r.stdout.splitlines() if ln.startswith("Train Epoch")])
+    assert len(outs[0]) == 12 and outs[0] == outs[1], (outs[0], outs[1])
+    # and they are a real trajectory, not a repeated or zero value
+    vals = [float(ln.split("loss=")[1]) for ln in outs[0]]
+    assert len(set(vals)) > 6 and min(vals) > 0.0
+
+
 def test_step_pipeline_matches_eager_steps():
     import pytorch_operator_b200 as pkg
     batches = [mo.synthetic_batch(64, 300 + i) for i in range(7)]
