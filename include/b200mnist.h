@@ -52,6 +52,13 @@ int b200mnist_version(void);
 /* Bytes of workspace the step entry points need for batches up to `max_batch`. */
 int64_t b200mnist_workspace_bytes(int max_batch);
 
+/* Where a step entry point leaves its saved activations inside the workspace (byte offset from its start, for a
+ * workspace sized for `max_batch`; -1 on a bad argument): which = 0 pooled conv1 output p1 [B,20,12,12] fp32,
+ * 1 its arg-max slots [B,20,12,12] uint8, 2 pooled conv2 output p2 [B,50,4,4] fp32 (= the [B,800] view of
+ * mnist.py:30), 3 its arg-max slots uint8, 4 fc1 output h [B,500] fp32, 5 log-probabilities [B,10] fp32.
+ * What autograd would have saved for mnist.py:42; the parity tests read them to teacher-force the oracle. */
+int64_t b200mnist_workspace_offset(int max_batch, int which);
+
 /* ---- whole-step entry points ----------------------------------------------------- */
 
 /* Replaces, for one batch, mnist.py:39-42: zero_grad(); output = model(data);
@@ -85,24 +92,46 @@ int b200mnist_forward_eval(const float *params, const float *x, const int64_t *t
 int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, int64_t n, float lr, float mu,
                            float grad_scale, int first_step, void *stream);
 
-/* Replaces DDP's gradient all_reduce (mnist.py:135-138) AND optimizer.step() (mnist.py:43) with one kernel
- * over NVLink peer memory: waits until every rank's gradient bucket is ready, reads all `world_size` buckets
- * (P2P loads), sums them in rank order (bit-identical on every rank), writes the sum to grads_sum and applies
- *   g = sum*grad_scale; buf = first_step ? g : mu*buf + g; p = p - lr*buf
- * over the whole flat bucket (B200MNIST_FLAT_ELEMS), then waits until every peer has finished reading.
- *   peer_grads_host[r]   : HOST array of world_size DEVICE pointers: rank r's gradient bucket as mapped in
- *                          this process (symmetric memory / CUDA IPC); entry [rank] is this rank's own bucket
- *   peer_signals_host[r] : same for each rank's signal pad (>= 64 uint32, zero-filled once)
- *   state                : 2 uint32 of local device memory, zero-filled once (epoch counter, CTA ticket)
- * Element range: the whole bucket except [skip_begin, skip_end) -- or, with only_skipped != 0, exactly that
- * range (both multiples of 4).  This lets a caller exchange fc1's gradient (93 % of the bucket, final as soon as
- * the fc backward kernel has run) on a side stream while the conv backward is still computing, and the rest
- * afterwards; the two calls must use different `state` words and different signal-pad regions.
- * Every rank must make the same calls in the same order; a call only enqueues work.  world_size in [2, 8]. */
-int b200mnist_allreduce_sgd(float *params, float *momentum, float *grads_sum, const float *const *peer_grads_host,
-                            uint32_t *const *peer_signals_host, int rank, int world_size, uint32_t *state,
-                            float lr, float mu, float grad_scale, int first_step, int64_t skip_begin, int64_t skip_end,
-                            int only_skipped, void *stream);
+/* ---- DDP exchange over NVLink peer memory ---------------------------------------------
+ * Replaces DDP's gradient all_reduce (mnist.py:135-138) AND optimizer.step() (mnist.py:43) for ranks on one
+ * NVLink-connected box, one process per GPU.  Every rank owns a PEER WINDOW: one device allocation
+ *   [ flag page B200MNIST_PEER_FLAG_BYTES | parameter bucket | gradient-sum bucket | staging bucket 0 | staging 1 ]
+ * (buckets of B200MNIST_FLAT_ELEMS floats) that the other ranks map through CUDA IPC.  The model's parameters and
+ * p.grad live in the window; the backward of step s writes its gradient into staging bucket (s & 1).
+ *
+ * Set-up (these allocate / map device memory and synchronise; call them once, outside any capture):
+ *   _create : cudaMalloc + zero-fill of a window on the current device; writes its address and a
+ *             B200MNIST_IPC_HANDLE_BYTES-byte handle (HOST buffers) to send to the other ranks' processes;
+ *   _open   : map another process's window from its handle (works for a GPU this process does not enumerate,
+ *             e.g. under CUDA_VISIBLE_DEVICES=<one GPU>, as long as the two GPUs can reach each other);
+ *   _close / _destroy : undo _open / _create;
+ *   _probe  : set-up check (one tiny kernel): out[r] (DEVICE, world_size uint32) = word
+ *             B200MNIST_PEER_PROBE_WORD of rank r's flag page, read through this process's mappings -- the path
+ *             the exchange kernels use. */
+#define B200MNIST_PEER_FLAG_BYTES 4096
+#define B200MNIST_IPC_HANDLE_BYTES 64
+#define B200MNIST_PEER_PROBE_WORD 192
+int64_t b200mnist_peer_window_bytes(void);
+int b200mnist_peer_window_create(void **window_out_host, void *ipc_handle_out_host);
+int b200mnist_peer_window_open(const void *ipc_handle_host, void **window_out_host);
+int b200mnist_peer_window_close(void *window);
+int b200mnist_peer_window_destroy(void *window);
+int b200mnist_peer_window_probe(void *const *windows_host, int world_size, uint32_t *out, void *stream);
+/* One half of the exchange + update of a step; enqueues one kernel, no allocation, capturable.
+ *   windows_host : HOST array of world_size window addresses as mapped in THIS process ([rank] = the local one)
+ *   parity       : which staging bucket holds this step's gradients (step & 1, the same on every rank)
+ *   momentum     : this rank's momentum bucket (local memory)
+ *   part 1: fc1.weight + fc1.bias (93 % of the bucket), two-shot: this rank reduces its 1/world_size slice over all
+ *           staging buckets in rank order, applies g = sum*grad_scale; buf = first_step ? g : mu*buf + g;
+ *           p = p - lr*buf, and stores the new parameters and the sum into every rank's window.  Meant for a side
+ *           stream, concurrent with b200mnist_forward_backward_phase(..., 2).  fc1's momentum is therefore
+ *           maintained on the slice's owner only.
+ *   part 2: everything else, one-shot: every rank reads all staging buckets, sums in rank order and updates its own
+ *           bucket; also waits until all ranks' part-1 slices have landed here.  Must follow the phase-2 call on
+ *           the same stream, and every step must issue exactly one part 1 and one part 2 (they share the step
+ *           epoch).  All ranks make the same calls in the same order; world_size in {2, 4, 8}. */
+int b200mnist_peer_exchange(void *const *windows_host, int rank, int world_size, int parity, float *momentum, float lr,
+                            float mu, float grad_scale, int first_step, int part, void *stream);
 
 /* b200mnist_forward_backward in two calls, for overlapping the gradient exchange with the backward pass:
  * phase 1 = forward, loss head and the fc backward (afterwards fc1.weight / fc1.bias gradients are final in
@@ -217,6 +246,12 @@ int b200mnist_event_record(void *event, void *stream);
  * in the HOST arrays.  delay_us > 0 first parks the stream for that long so the following
  * launches queue up (no host launch gaps inside the timings).  Not for use under capture. */
 long long b200mnist_launch_count(void);
+/* b200mnist_delay: parks `stream` for delay_us microseconds (one spinning thread) so that launches issued behind it
+ * queue up.  b200mnist_fma_peak: a register-resident packed-FMA (fma.rn.f32x2) loop on `blocks` CTAs of 256 threads,
+ * no memory traffic; `out` needs blocks*256 floats; returns the FLOPs the launch performs (blocks*256*64*iters), or a
+ * negative error.  Timed by tools/measure_peaks.py to get the fp32 FMA roofline of this GPU. */
+int b200mnist_delay(void *stream, int delay_us);
+int64_t b200mnist_fma_peak(float *out, int blocks, int iters, void *stream);
 int b200mnist_profile_begin(void *stream, int delay_us);
 int b200mnist_profile_end(float *ms_out_host, const char **names_out_host, int cap, void *stream);
 

@@ -69,12 +69,19 @@ SIGNATURES = {
     "b200mnist_last_error": (ctypes.c_char_p, []),
     "b200mnist_version": (_i32, []),
     "b200mnist_workspace_bytes": (_i64, [_i32]),
+    "b200mnist_workspace_offset": (_i64, [_i32, _i32]),
     "b200mnist_forward_backward": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _c_f]),
     "b200mnist_train_step": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _f32, _f32, _i32, _c_f, _c_f]),
     "b200mnist_forward_eval": (_i32, [_c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _c_f]),
     "b200mnist_sgd_momentum": (_i32, [_c_f, _c_f, _c_f, _i64, _f32, _f32, _f32, _i32, _c_f]),
-    "b200mnist_allreduce_sgd": (_i32, [_c_f, _c_f, _c_f, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
-                                       _i32, _i32, _c_f, _f32, _f32, _f32, _i32, _i64, _i64, _i32, _c_f]),
+    "b200mnist_peer_window_bytes": (_i64, []),
+    "b200mnist_peer_window_create": (_i32, [ctypes.POINTER(ctypes.c_void_p), _c_f]),
+    "b200mnist_peer_window_open": (_i32, [_c_f, ctypes.POINTER(ctypes.c_void_p)]),
+    "b200mnist_peer_window_close": (_i32, [_c_f]),
+    "b200mnist_peer_window_destroy": (_i32, [_c_f]),
+    "b200mnist_peer_window_probe": (_i32, [ctypes.POINTER(ctypes.c_void_p), _i32, _c_f, _c_f]),
+    "b200mnist_peer_exchange": (_i32, [ctypes.POINTER(ctypes.c_void_p), _i32, _i32, _i32, _c_f, _f32, _f32, _f32, _i32,
+                                       _i32, _c_f]),
     "b200mnist_forward_backward_phase": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv1_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv2_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
@@ -97,6 +104,8 @@ SIGNATURES = {
     "b200mnist_stage_inputs": (_i32, [_c_f, _c_f, _i64, _c_f, _c_f, _c_f, _c_f]),
     "b200mnist_event_record": (_i32, [_c_f, _c_f]),
     "b200mnist_launch_count": (ctypes.c_longlong, []),
+    "b200mnist_delay": (_i32, [_c_f, _i32]),
+    "b200mnist_fma_peak": (_i64, [_c_f, _i32, _i32, _c_f]),
     "b200mnist_profile_begin": (_i32, [_c_f, _i32]),
     "b200mnist_profile_end": (_i32, [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), _i32, _c_f]),
 }

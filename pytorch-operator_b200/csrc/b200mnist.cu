@@ -12,7 +12,7 @@
 #include "conv_fwd.cuh"
 #include "fc.cuh"
 #include "optim.cuh"
-#include "peer_allreduce.cuh"
+#include "peer_exchange.cuh"
 #include "tc_gemm.cuh"
 #include "tc_conv_bwd.cuh"
 
@@ -506,6 +506,14 @@ int64_t b200mnist_workspace_bytes(int max_batch) {
     return (int64_t)carve(nullptr, max_batch).bytes;
 }
 
+int64_t b200mnist_workspace_offset(int max_batch, int which) {
+    if (max_batch < 1 || max_batch > 65536) return -1;
+    const Workspace w = carve(reinterpret_cast<void *>(uintptr_t(256)), max_batch);   // non-null base: offsets + 256
+    const void *p[] = {w.p1, w.i1, w.p2, w.i2, w.h, w.logp};
+    if (which < 0 || which >= 6) return -1;
+    return (int64_t)(reinterpret_cast<uintptr_t>(p[which]) - 256);
+}
+
 int b200mnist_forward_backward(const float *params, float *grads, const float *x, const int64_t *target, int B,
                                void *workspace, int64_t workspace_bytes, float *loss_out, float *logp_out,
                                void *stream) {
@@ -577,38 +585,109 @@ int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, i
                       static_cast<cudaStream_t>(stream));
 }
 
-int b200mnist_allreduce_sgd(float *params, float *momentum, float *grads_sum, const float *const *peer_grads_host,
-                            uint32_t *const *peer_signals_host, int rank, int world_size, uint32_t *state,
-                            float lr, float mu, float grad_scale, int first_step, int64_t skip_begin, int64_t skip_end,
-                            int only_skipped, void *stream) {
-    if (!params || !momentum || !grads_sum || !peer_grads_host || !peer_signals_host || !state)
-        return fail_arg(1, "null pointer argument");
-    if (world_size < 2 || world_size > kMaxPeers || rank < 0 || rank >= world_size)
-        return fail_arg(2, "world_size must be in [2, 8] and rank in [0, world_size)");
-    PeerArgs pa{};
-    for (int r = 0; r < world_size; ++r) {
-        if (!peer_grads_host[r] || !peer_signals_host[r]) return fail_arg(1, "null peer pointer");
-        if (!aligned16(peer_grads_host[r])) return fail_arg(3, "peer gradient buckets must be 16-byte aligned");
-        pa.grads[r] = peer_grads_host[r];
-        pa.signals[r] = peer_signals_host[r];
+/* ---- peer windows: set-up calls (these allocate / map; they are not stream work) ---- */
+int64_t b200mnist_peer_window_bytes(void) { return (int64_t)kPeerWindowBytes; }
+
+int b200mnist_peer_window_create(void **window_out_host, void *ipc_handle_out_host) {
+    if (!window_out_host || !ipc_handle_out_host) return fail_arg(1, "null pointer argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == B200MNIST_IPC_HANDLE_BYTES, "IPC handle size");
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, kPeerWindowBytes);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc(peer window)");
+    e = cudaMemset(p, 0, kPeerWindowBytes);
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return fail_cuda(e, "cudaIpcGetMemHandle(peer window)");
     }
-    if (!aligned16(params) || !aligned16(momentum) || !aligned16(grads_sum))
-        return fail_arg(3, "params/momentum/grads_sum must be 16-byte aligned");
-    if (skip_begin < 0 || skip_end < skip_begin || skip_end > kFlatElems || (skip_begin & 3) || (skip_end & 3))
-        return fail_arg(2, "skip range must lie in the bucket and be a multiple of 4 elements");
-    pa.rank = rank;
-    pa.world = world_size;
-    // element range handled by this call: [skip_begin, skip_end) if only_skipped, else everything but that range
-    const int lo = only_skipped ? (int)skip_begin : 0;
-    const int n = only_skipped ? (int)skip_end : kFlatElems;
-    const int hole_lo = only_skipped ? n : (int)skip_begin, hole_hi = only_skipped ? n : (int)skip_end;
-    const int count = (n - lo) - (hole_hi - hole_lo);
-    if (count <= 0) return 0;
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    allreduce_sgd_kernel<<<ceil_div(count, 1024), 256, 0, s>>>(pa, params, momentum, grads_sum, lo, hole_lo, hole_hi, n,
-                                                               -lr, mu, grad_scale, first_step, state, state + 1);
-    CHECK_LAUNCH("peer-memory all-reduce + sgd", s);
+    memcpy(ipc_handle_out_host, &h, sizeof(h));
+    *window_out_host = p;
     return 0;
+}
+int b200mnist_peer_window_open(const void *ipc_handle_host, void **window_out_host) {
+    if (!ipc_handle_host || !window_out_host) return fail_arg(1, "null pointer argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle_host, sizeof(h));
+    void *p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail_cuda(e, "cudaIpcOpenMemHandle(peer window)");
+    }
+    *window_out_host = p;
+    return 0;
+}
+int b200mnist_peer_window_close(void *window) {
+    if (!window) return 0;
+    cudaError_t e = cudaIpcCloseMemHandle(window);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaIpcCloseMemHandle");
+    return 0;
+}
+int b200mnist_peer_window_destroy(void *window) {
+    if (!window) return 0;
+    cudaError_t e = cudaFree(window);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaFree(peer window)");
+    return 0;
+}
+int b200mnist_peer_window_probe(void *const *windows_host, int world_size, uint32_t *out, void *stream) {
+    if (!windows_host || !out) return fail_arg(1, "null pointer argument");
+    if (world_size < 1 || world_size > kMaxPeers) return fail_arg(2, "world_size must be in [1, 8]");
+    PeerWin pw{};
+    for (int r = 0; r < world_size; ++r) {
+        if (!windows_host[r]) return fail_arg(1, "null peer window");
+        pw.base[r] = static_cast<char *>(windows_host[r]);
+    }
+    pw.world = world_size;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    peer_probe_kernel<<<1, 32, 0, s>>>(pw, out);
+    CHECK_LAUNCH("peer window probe", s);
+    return 0;
+}
+
+}  // extern "C"
+namespace {
+template <int WORLD>
+int launch_peer(const PeerWin &pw, float *m, int parity, float lr, float mu, float scale, int first, int part,
+                cudaStream_t s) {
+    if (part == 1) {
+        // 64-thread CTAs at <= 64 registers, at most one per SM: 4096 registers, which is what two CTAs of the conv2
+        // backward kernel leave free on an SM -- the exchange sits beside its single wave instead of splitting it
+        constexpr int per = (kFc1Vec4 + WORLD - 1) / WORLD;
+        const int grid = clampi(ceil_div(per, kPeerFc1Threads), 1, 148);
+        peer_fc1_kernel<WORLD><<<grid, kPeerFc1Threads, 0, s>>>(pw, m, parity, -lr, mu, scale, first);
+        CHECK_LAUNCH("peer exchange: fc1 slice reduce + sgd + push (NVLink P2P)", s);
+    } else {
+        CHECK_PDL(launch_pdl(peer_rest_kernel<WORLD>, dim3(ceil_div(kRestVec4, kPeerRestThreads)), dim3(kPeerRestThreads),
+                             0, s, pw, m, parity, -lr, mu, scale, first),
+                  "peer exchange: conv/fc2 all-reduce + sgd (NVLink P2P)", s);
+    }
+    return 0;
+}
+}  // namespace
+extern "C" {
+
+int b200mnist_peer_exchange(void *const *windows_host, int rank, int world_size, int parity, float *momentum, float lr,
+                            float mu, float grad_scale, int first_step, int part, void *stream) {
+    if (!windows_host || !momentum) return fail_arg(1, "null pointer argument");
+    if ((world_size != 2 && world_size != 4 && world_size != 8) || rank < 0 || rank >= world_size)
+        return fail_arg(2, "world_size must be 2, 4 or 8 and rank in [0, world_size)");
+    if ((parity != 0 && parity != 1) || (part != 1 && part != 2)) return fail_arg(2, "parity must be 0/1 and part 1/2");
+    if (!aligned16(momentum)) return fail_arg(3, "momentum must be 16-byte aligned");
+    PeerWin pw{};
+    for (int r = 0; r < world_size; ++r) {
+        if (!windows_host[r] || (reinterpret_cast<uintptr_t>(windows_host[r]) & 255u))
+            return fail_arg(3, "peer windows must be non-null and 256-byte aligned");
+        pw.base[r] = static_cast<char *>(windows_host[r]);
+    }
+    pw.rank = rank;
+    pw.world = world_size;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    switch (world_size) {
+    case 2: return launch_peer<2>(pw, momentum, parity, lr, mu, grad_scale, first_step, part, s);
+    case 4: return launch_peer<4>(pw, momentum, parity, lr, mu, grad_scale, first_step, part, s);
+    default: return launch_peer<8>(pw, momentum, parity, lr, mu, grad_scale, first_step, part, s);
+    }
 }
 
 int b200mnist_conv1_relu_pool_fwd(const float *x, const float *w, const float *bias, float *out, uint8_t *idx, int B,
@@ -864,6 +943,24 @@ int b200mnist_profile_begin(void *stream, int delay_us) {
     cudaError_t e = cudaEventRecord(g_prof.ev[0], s);
     if (e != cudaSuccess) return fail_cuda(e, "cudaEventRecord");
     return 0;
+}
+
+int b200mnist_delay(void *stream, int delay_us) {
+    if (delay_us <= 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    delay_kernel<<<1, 1, 0, s>>>((unsigned long long)delay_us * 1000ull);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail_cuda(e, "delay kernel");
+    return 0;
+}
+
+int64_t b200mnist_fma_peak(float *out, int blocks, int iters, void *stream) {
+    if (!out || blocks < 1 || iters < 1) return fail_arg(1, "out null or blocks/iters < 1");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    fma_peak_kernel<<<blocks, 256, 0, s>>>(out, iters, 1.0000001f, 0.9999999f);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail_cuda(e, "fma peak kernel");
+    return (int64_t)blocks * 256 * 64 * iters;
 }
 
 int b200mnist_profile_end(float *ms_out_host, const char **names_out_host, int cap, void *stream) {

@@ -186,6 +186,25 @@ __global__ void delay_kernel(unsigned long long ns) {
     } while (t - t0 < ns);
 }
 
+// Register-resident FFMA2 loop: the fp32 roofline the SIMT kernels are measured against (bench.py).  Each thread
+// keeps 16 independent float2 accumulators (32 FMA chains), `iters` passes of 16 packed FMAs, no memory traffic;
+// 2 x 2 x 16 x iters FLOP per thread.  The result is stored so nothing is optimised away.
+__global__ void __launch_bounds__(256) fma_peak_kernel(float *out, int iters, float a, float b) {
+    float2 acc[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) acc[j] = make_float2(a + (float)j, b - (float)j + (float)threadIdx.x);
+    const float2 x = make_float2(a, b), y = make_float2(b, a);
+#pragma unroll 8
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc[j] = __ffma2_rn(acc[j], x, y);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s += acc[j].x + acc[j].y;
+    out[blockIdx.x * 256 + threadIdx.x] = s;
+}
+
 // Input pipeline (mnist.py:118-125): gather a batch of 28x28 uint8 images by index and apply ToTensor +
 // Normalize -- x/255, then (x - mean)/std, each an IEEE fp32 rounding like the reference's CPU ops -- plus the
 // matching labels.  One CTA per image, 196 threads x 4 pixels (32-bit load, 128-bit store).

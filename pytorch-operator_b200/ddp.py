@@ -3,16 +3,25 @@
 rank 0's parameters are broadcast at construction and every backward leaves the cross-rank
 gradient in place.  Two exchange paths, both over ONE flat 1.7 MB gradient bucket:
 
-* fused (default on one NVLink-connected box): the step's gradient is written into a
-  symmetric-memory bucket every peer has mapped, and ``b200mnist_allreduce_sgd`` -- one kernel --
-  reads all ranks' buckets over NVLink, sums them in rank order, and applies the SGD update with
-  1/world_size folded in (no NCCL call, no separate optimizer launch);
+* fused (default for 2/4/8 ranks on one NVLink-connected box): every rank owns a *peer window* -- one
+  device allocation holding its parameter bucket, gradient-sum bucket (p.grad) and two staging gradient
+  buckets -- that all other ranks map through CUDA IPC (``b200mnist_peer_window_*``; this works with one
+  process per GPU under ``CUDA_VISIBLE_DEVICES=<rank>``, the single-GPU-per-pod view, as well as with all
+  GPUs visible).  ``b200mnist_peer_exchange`` then replaces all_reduce + optimizer.step(): fc1's 93 % of the
+  bucket is reduced two-shot (each rank sums its 1/world slice in rank order, applies SGD and stores the new
+  parameters into every window) on a side stream WHILE the conv backward runs; the small remainder is
+  reduced one-shot at the end of the step.  No NCCL call, no separate optimizer launch.  fc1's momentum is
+  kept by each slice's owner only (``flat_momentum`` holds this rank's slice of it).
 * NCCL: ``all_reduce(SUM)`` of the bucket on the process group, then the fused SGD kernel with
   ``grad_scale = 1/world_size`` (also what the autograd-bridge path and gloo/CPU host tests use).
+
+Which path a job takes is decided collectively at construction (every rank takes the same one) and
+logged once on rank 0 with the reason.
 """
 from __future__ import annotations
 
 import ctypes
+import logging
 
 import torch
 import torch.distributed as dist
@@ -21,7 +30,27 @@ import torch.nn as nn
 from . import _cabi
 from .net import Net, _stream
 
-_PAD_OFFSET_BYTES = 8192  # our flags live at the end of the 9 KiB signal pad, away from torch's own channels
+log = logging.getLogger("pytorch_operator_b200.ddp")
+_IPC_BYTES = 64
+_FLAG_BYTES = 4096
+_PROBE_WORD = 192  # include/b200mnist.h: B200MNIST_PEER_PROBE_WORD
+
+
+class _DeviceMemory:
+    """Zero-copy torch view of raw device memory (``__cuda_array_interface__``)."""
+
+    def __init__(self, ptr: int, count: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": typestr, "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+def _view(ptr: int, count: int, dtype, device) -> torch.Tensor:
+    """A tensor over memory of THIS rank's own window (never a peer's mapping)."""
+    typestr = {torch.float32: "<f4", torch.int32: "<i4"}[dtype]
+    t = torch.as_tensor(_DeviceMemory(ptr, count, typestr), device=device)
+    if t.data_ptr() != ptr or t.dtype != dtype:
+        raise RuntimeError("could not view the peer window as a tensor without a copy")
+    return t
 
 
 class DistributedDataParallel(nn.Module):
@@ -39,76 +68,176 @@ class DistributedDataParallel(nn.Module):
         dist.broadcast(module.flat_params, src=0, group=process_group)  # DDP ctor semantics
         self.fused = False
         self.fused_error = None
+        self._windows = None
+        self._opened = []
+        self._step = 0              # steps taken on the fused path: step & 1 selects the staging bucket
+        self._force_parity = None   # set while a StepGraph captures one of its two variants
+        self.timeline = None        # set to a dict to have the next eager fused step record its phase boundaries
         want = fused if fused is not None else True
-        if want and module.device.type == "cuda" and 2 <= self.world_size <= 8 \
-                and dist.get_backend(process_group) == "nccl":
-            try:
-                self._setup_fused()
-                self.fused = True
-            except Exception as e:  # no peer access / symmetric memory unavailable: NCCL path
-                self.fused_error = repr(e)
-                if fused:
-                    raise
-        # every rank must take the same path
-        flag = torch.tensor([1 if self.fused else 0], device=module.device if module.device.type == "cuda" else "cpu")
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=process_group)
-        self.fused = bool(flag.item())
+        eligible = (want and module.device.type == "cuda" and self.world_size in (2, 4, 8)
+                    and dist.get_backend(process_group) == "nccl")
+        if eligible:
+            self._setup_fused()
+        elif want and fused:
+            self.fused_error = "fused exchange needs CUDA, the nccl backend and 2, 4 or 8 ranks"
+        if self.rank == 0:
+            if self.fused:
+                log.info("DDP exchange: fused peer-window kernels over NVLink (CUDA IPC), %d ranks", self.world_size)
+            else:
+                log.info("DDP exchange: %s all_reduce + SGD kernel%s", dist.get_backend(process_group),
+                         "" if self.fused_error is None else " (fused path unavailable: %s)" % self.fused_error)
+        if fused and not self.fused:
+            raise RuntimeError("fused DDP exchange unavailable: %s" % self.fused_error)
+
+    # ---- fused set-up: every decision that can differ between ranks is agreed on before the next step ----
+    def _agree(self, ok: bool, err):
+        """all ranks succeed or none does; returns the agreed outcome (and keeps the first local error text)."""
+        if not ok and self.fused_error is None:
+            self.fused_error = repr(err)
+        flag = torch.tensor([1 if ok else 0], device=self.module.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.process_group)
+        agreed = bool(flag.item())
+        if not agreed and self.fused_error is None:
+            self.fused_error = "another rank could not set up its peer window"
+        return agreed
 
     def _setup_fused(self):
-        import torch.distributed._symmetric_memory as symm
-        net, ws = self.module, self.world_size
-        group = self.process_group if self.process_group is not None else dist.group.WORLD
-        self._staging = symm.empty(net.flat_grads.numel(), dtype=torch.float32, device=net.device)
-        self._staging.zero_()
-        self._symm = symm.rendezvous(self._staging, group)
-        if int(getattr(self._symm, "signal_pad_size", 0)) < _PAD_OFFSET_BYTES + 256:
-            raise RuntimeError("signal pad too small")
-        self._peer_grads = (ctypes.c_void_p * ws)(*[int(p) for p in self._symm.buffer_ptrs])
-        self._peer_signals = (ctypes.c_void_p * ws)(*[int(p) + _PAD_OFFSET_BYTES for p in self._symm.signal_pad_ptrs])
-        self._state = torch.zeros(4, dtype=torch.int32, device=net.device)   # two exchange instances x (epoch, ticket)
-        self._peer_signals_b = (ctypes.c_void_p * ws)(*[int(p) + _PAD_OFFSET_BYTES + 256 for p in self._symm.signal_pad_ptrs])
-        L = _cabi.lib()
-        self._fc1_range = (int(L.b200mnist_tensor_offset(4)), int(L.b200mnist_tensor_offset(6)))
-        self._side = torch.cuda.Stream(device=net.device)
-        self._ev_fc, self._ev_side = torch.cuda.Event(), torch.cuda.Event()
-        torch.cuda.synchronize(net.device)
+        net, ws, L = self.module, self.world_size, _cabi.lib()
+        dev = net.device
+        own, handle, err = ctypes.c_void_p(), (ctypes.c_char * _IPC_BYTES)(), None
+        try:  # 1. local: allocate the window and export it
+            with torch.cuda.device(dev):
+                _cabi.check(L.b200mnist_peer_window_create(ctypes.byref(own), handle), "peer_window_create")
+        except Exception as e:
+            err = e
+        if not self._agree(err is None, err):
+            if own.value:
+                L.b200mnist_peer_window_destroy(own)
+            return
+        # 2. exchange the handles over the process group (the env:// rendezvous the operator set up) and map the peers
+        handles = [None] * ws
+        dist.all_gather_object(handles, bytes(handle.raw), group=self.process_group)
+        ptrs, opened = [0] * ws, []
+        try:
+            with torch.cuda.device(dev):
+                for r in range(ws):
+                    if r == self.rank:
+                        ptrs[r] = own.value
+                        continue
+                    p = ctypes.c_void_p()
+                    _cabi.check(L.b200mnist_peer_window_open(handles[r], ctypes.byref(p)), f"peer_window_open(rank {r})")
+                    ptrs[r] = p.value
+                    opened.append(p.value)
+            # 3. verify each mapping: every rank stamps its own window, then reads all stamps through the mappings
+            _view(own.value + 4 * _PROBE_WORD, 1, torch.int32, dev).fill_(1000 + self.rank)
+            torch.cuda.synchronize(dev)
+        except Exception as e:
+            err = e
         dist.barrier(group=self.process_group)
+        if err is None:
+            try:
+                got = torch.zeros(ws, dtype=torch.int32, device=dev)
+                _cabi.check(L.b200mnist_peer_window_probe((ctypes.c_void_p * ws)(*ptrs), ws, got.data_ptr(), _stream()),
+                            "peer_window_probe")
+                got = got.tolist()
+                if got != [1000 + r for r in range(ws)]:
+                    raise RuntimeError(f"peer windows read back {got}")
+            except Exception as e:
+                err = e
+        if not self._agree(err is None, err):
+            with torch.cuda.device(dev):
+                for p in opened:
+                    L.b200mnist_peer_window_close(p)
+                dist.barrier(group=self.process_group)
+                L.b200mnist_peer_window_destroy(own)
+            return
+        # 4. move the model into the window: parameters and p.grad become views of window memory
+        n = net.flat_params.numel()
+        bucket = 4 * n
+        assert int(L.b200mnist_peer_window_bytes()) == _FLAG_BYTES + 4 * bucket
+        params = _view(own.value + _FLAG_BYTES, n, torch.float32, dev)
+        gsum = _view(own.value + _FLAG_BYTES + bucket, n, torch.float32, dev)
+        params.copy_(net.flat_params)
+        gsum.copy_(net.flat_grads)
+        net._bind(params, gsum, net.flat_momentum)
+        self._staging = [_view(own.value + _FLAG_BYTES + (2 + k) * bucket, n, torch.float32, dev) for k in (0, 1)]
+        self._windows = (ctypes.c_void_p * ws)(*ptrs)
+        self._own_window, self._opened = own, opened
+        self._side = torch.cuda.Stream(device=dev)
+        self._ev_fc, self._ev_side = torch.cuda.Event(), torch.cuda.Event()
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=self.process_group)
+        self.fused = True
+
+    def close(self):
+        """Unmap the peers' windows and free this rank's (collective; call before destroy_process_group()).  The
+        model's buckets move back to ordinary device memory first, so the model stays usable (NCCL path)."""
+        if not self.fused:
+            return
+        net, L = self.module, _cabi.lib()
+        net.release_graphs()
+        torch.cuda.synchronize(net.device)
+        net._bind(net.flat_params.clone(), net.flat_grads.clone(), net.flat_momentum)
+        self.fused, self._staging, self._windows = False, None, None
+        dist.barrier(group=self.process_group)
+        with torch.cuda.device(net.device):
+            for p in self._opened:
+                L.b200mnist_peer_window_close(p)
+            dist.barrier(group=self.process_group)
+            L.b200mnist_peer_window_destroy(self._own_window)
+        self._opened = []
 
     # ---- exchange paths ----
     def reduce_gradients(self):
         """NCCL path: sum the flat gradient bucket over all ranks, in place, on the current stream."""
         dist.all_reduce(self.module.flat_grads, op=dist.ReduceOp.SUM, group=self.process_group)
 
-    def _allreduce_sgd(self, optimizer, signals, state_ptr, only_fc1):
+    def _exchange(self, optimizer, parity, part):
         m = self.module
-        _cabi.check(_cabi.lib().b200mnist_allreduce_sgd(
-            m.flat_params.data_ptr(), m.flat_momentum.data_ptr(), m.flat_grads.data_ptr(), self._peer_grads,
-            signals, self.rank, self.world_size, state_ptr, optimizer.lr, optimizer.momentum,
-            1.0 / self.world_size, 1 if optimizer.first_step else 0, self._fc1_range[0], self._fc1_range[1],
-            1 if only_fc1 else 0, _stream()), "allreduce_sgd")
+        _cabi.check(_cabi.lib().b200mnist_peer_exchange(
+            self._windows, self.rank, self.world_size, parity, m.flat_momentum.data_ptr(), optimizer.lr,
+            optimizer.momentum, 1.0 / self.world_size, 1 if optimizer.first_step else 0, part, _stream()),
+            "peer_exchange")
 
     def fused_train_step(self, x, target, optimizer, loss_out=None):
-        """Fused path.  The gradient is produced into the symmetric staging bucket in two phases; fc1's part
-        (93 % of the bucket, final after the fc backward kernel) is exchanged + applied by the peer-memory kernel
-        on a side stream WHILE the conv backward runs, the remainder right after it.  Peers' staged gradients ->
-        rank-ordered sum in flat_grads -> SGD update, 1/world_size folded in."""
+        """Fused path.  The gradient is produced into this step's staging bucket in two phases; fc1's part
+        (93 % of the bucket, final after the fc backward kernel) is exchanged + applied by the two-shot peer kernel
+        on a side stream WHILE the conv backward runs, the remainder right after it."""
         net = self.module
         cur = torch.cuda.current_stream()
-        net.forward_backward_phase(x, target, 1, self._staging, loss_out)
+        capturing = self._force_parity is not None
+        parity = self._force_parity if capturing else self._step & 1
+        staging = self._staging[parity]
+        tl = None if capturing else self.timeline
+
+        def mark(key, stream):
+            if tl is not None:
+                tl[key] = torch.cuda.Event(enable_timing=True)
+                tl[key].record(stream)
+
+        mark("start", cur)
+        net.forward_backward_phase(x, target, 1, staging, loss_out)
+        mark("phase1_end", cur)
         self._ev_fc.record(cur)
         self._side.wait_event(self._ev_fc)
         with torch.cuda.stream(self._side):
-            self._allreduce_sgd(optimizer, self._peer_signals, self._state.data_ptr(), only_fc1=True)
+            self._exchange(optimizer, parity, 1)
+            mark("fc1_exchange_end", self._side)
             self._ev_side.record(self._side)
-        loss = net.forward_backward_phase(x, target, 2, self._staging, loss_out)
-        self._allreduce_sgd(optimizer, self._peer_signals_b, self._state.data_ptr() + 8, only_fc1=False)
+        loss = net.forward_backward_phase(x, target, 2, staging, loss_out)
+        mark("phase2_end", cur)
+        self._exchange(optimizer, parity, 2)
+        mark("rest_exchange_end", cur)
         cur.wait_event(self._ev_side)
         optimizer.first_step = False
+        if not capturing:
+            self._step += 1
         return loss
 
     @property
     def staging(self):
-        return self._staging if self.fused else None
+        """The staging bucket the NEXT fused step writes this rank's gradient into (None on the NCCL path)."""
+        return self._staging[self._step & 1] if self.fused else None
 
     def forward(self, x):
         return self.module(x)

@@ -13,7 +13,9 @@ instead of the MNIST download, which needs a network), ``--data-root``, ``--no-g
 from __future__ import print_function
 
 import argparse
+import logging
 import os
+import sys
 
 import torch
 import torch.distributed as dist
@@ -152,6 +154,7 @@ def main(argv=None):
     parser.add_argument('--no-graph', action='store_true', default=False,
                         help='do not capture the training step in a CUDA graph')
     args = parser.parse_args(argv)
+    logging.basicConfig(level=logging.INFO, stream=sys.stderr)  # stdout stays the reference's lines only
     use_cuda = not args.no_cuda and torch.cuda.is_available()
     if use_cuda:
         print('Using CUDA')
@@ -208,6 +211,7 @@ def main(argv=None):
     if is_distributed():
         model.release_graphs()  # graphs that captured NCCL kernels must go before the process group
         getattr(model, "_b200_step_graphs", {}).clear()
+        model.close()           # unmap / free the peer windows of the fused exchange (no-op on the NCCL path)
         dist.barrier()
         dist.destroy_process_group()
 

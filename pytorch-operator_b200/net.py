@@ -299,7 +299,6 @@ class StepGraph:
         model._check_inputs(self.x, self.target)
         self.lr, self.momentum = optimizer.lr, optimizer.momentum
         model.workspace(batch)  # allocate outside capture
-        self.graph = torch.cuda.CUDAGraph()
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream())
         # Warm-up on the capture stream (lazy CUDA/NCCL initialisation must happen outside the
@@ -312,26 +311,45 @@ class StepGraph:
         for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum), saved):
             t.copy_(sv)
         torch.cuda.synchronize(dev)
-        # thread_local: the NCCL watchdog thread may query its own events while this thread captures
-        # (in the default global mode that query invalidates the capture and the ranks dead-lock)
-        with torch.cuda.graph(self.graph, stream=side, capture_error_mode="thread_local"):
-            self.loss = model.train_step(self.x, self.target, optimizer, loss_out=loss_out)
-            if loss_host is not None:  # D2H memcpy node: every replay leaves the step's loss in pinned host memory
-                loss_host.copy_(self.loss.reshape(1), non_blocking=True)
+        # Under the fused DDP exchange a step writes its gradient into staging bucket (step & 1): the kernel
+        # arguments differ between even and odd steps, so both variants are captured and replay() alternates.
+        ddp = model._ddp
+        self._ddp = ddp if (ddp is not None and ddp.fused) else None
+        self.graphs = []
+        for variant in range(2 if self._ddp is not None else 1):
+            g = torch.cuda.CUDAGraph()
+            if self._ddp is not None:
+                self._ddp._force_parity = variant
+            try:
+                # thread_local: the NCCL watchdog thread may query its own events while this thread captures
+                # (in the default global mode that query invalidates the capture and the ranks dead-lock)
+                with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                    self.loss = model.train_step(self.x, self.target, optimizer, loss_out=loss_out)
+                    if loss_host is not None:  # D2H memcpy node: every replay leaves the step's loss in pinned host memory
+                        loss_host.copy_(self.loss.reshape(1), non_blocking=True)
+            finally:
+                if self._ddp is not None:
+                    self._ddp._force_parity = None
+            self.graphs.append(g)
         self.loss_host = loss_host
         model._graphs.append(weakref.ref(self))
 
     def release(self):
-        """Destroy the captured graph.  A graph that captured NCCL kernels must be gone before
+        """Destroy the captured graphs.  A graph that captured NCCL kernels must be gone before
         ``destroy_process_group()``, which otherwise blocks forever."""
-        if self.graph is not None:
-            self.graph.reset()
-            self.graph = None
+        for g in self.graphs:
+            g.reset()
+        self.graphs = []
 
     def replay(self):
         if (self.optimizer.lr, self.optimizer.momentum) != (self.lr, self.momentum):
             raise RuntimeError("lr/momentum changed after capture; build a new StepGraph")
-        self.graph.replay()
+        if self._ddp is not None:
+            variant = self._ddp._step & 1
+            self._ddp._step += 1
+        else:
+            variant = 0
+        self.graphs[variant].replay()
         return self.loss
 
 

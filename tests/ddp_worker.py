@@ -1,94 +1,60 @@
-"""Worker for tests/test_gpu_multi.py: one rank of a world_size-2 DDP run on two GPUs (NCCL),
-launched with the operator's env contract.  Replays the reference's ws=2 fixture (2 free-running
-steps, per-rank batches) and checks losses, averaged gradients and parameters; then runs the
-smoke-dist send/recv + all_reduce check.  Exit code 0 = pass."""
+"""Multi-GPU DDP parity checks (one rank's share; NCCL process group already initialised).
+
+Used twice: as the worker script of tests/test_gpu_multi.py (launched with the operator's env contract), and by
+bench.py's parity prologue at N>1, which puts the outcome on the driver's record.  Every check raises
+AssertionError on a mismatch.
+
+  * ``fixture_run``  -- world_size 2: replays the fixture the unmodified reference produced with
+    DistributedDataParallelCPU on gloo (tests/golden/train_ws2_b64.npz; 2 free-running steps, per-rank batches) and
+    checks losses, averaged gradients and parameters (mnist.py:135-138,39-43);
+  * ``property_run`` -- any world size: no reference fixture exists beyond ws=2, so check what must hold for every
+    ws -- the bucket every rank ends up with is the rank-ordered sum of the per-rank gradients (recomputed from an
+    all_gather), all replicas stay bit-identical, the loss decreases;
+  * ``smoke_dist_run`` -- dist_sendrecv.py:15-34 (send/recv star + square, bit-exact) and the all_reduce
+    bit-exactness check.
+"""
 import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT)
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
 
 import torch
 import torch.distributed as dist
 
 import pytorch_operator_b200 as pkg
 from pytorch_operator_b200 import dist_sendrecv
-from tests.helpers import RTOL, golden_batch, golden_tensor_check, load_golden
+from tests.helpers import RTOL, golden_tensor_check, load_golden
 
 
-def property_run(mode):
-    """Any world size (2/4/8): no reference fixture exists for ws > 2, so check what must hold for every ws --
-    the bucket every rank ends up with is the rank-ordered sum of the per-rank gradients (recomputed here from an
-    all_gather), all replicas stay bit-identical, and the loss decreases over a few steps."""
-    rank, ws = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    dev = torch.device("cuda", 0 if torch.cuda.device_count() == 1 else rank)
-    torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev)
-    from oracle import mnist_oracle as mo
-    torch.manual_seed(1)
-    net = pkg.Net().to(dev)
-    model = pkg.DistributedDataParallel(net, fused=mode.startswith("prop-fused"))
-    opt = pkg.SGD(model.parameters(), lr=0.01, momentum=0.5)
-    losses = []
-    for s in range(6):
-        x, t = mo.synthetic_batch(64, 5000 + 31 * s + rank)
-        local = pkg.Net().to(dev)                      # this rank's own gradient, without any exchange
-        local.flat_params.copy_(net.flat_params)
-        local.forward_backward(x.to(dev), t.to(dev))
-        gathered = [torch.empty_like(local.flat_grads) for _ in range(ws)]
-        dist.all_gather(gathered, local.flat_grads)
-        want = gathered[0].clone()
-        for r in range(1, ws):
-            want += gathered[r]                        # rank order, like the fused kernel
-        losses.append(float(model.train_step(x.to(dev), t.to(dev), opt)))
-        if model.fused:
-            assert torch.equal(net.flat_grads, want), f"step {s}: fused sum differs from the rank-ordered sum"
-        else:
-            torch.testing.assert_close(net.flat_grads, want, rtol=1e-5, atol=1e-7)   # NCCL's own summation order
-        ref = net.flat_params.clone()
-        dist.broadcast(ref, src=0)
-        assert torch.equal(ref, net.flat_params), f"step {s}: replicas diverged"
-    lt = torch.tensor([losses[0], losses[-1]], device=dev)
-    dist.all_reduce(lt)
-    assert float(lt[1]) < float(lt[0]), losses
-    rows = dist_sendrecv.allreduce_check(sizes=(4, 431296, 1 << 22), iters=5)
-    assert all(r["bit_exact"] for r in rows)
-    torch.manual_seed(0)
-    dist_sendrecv.run()
-    model.release_graphs()
-    dist.barrier()
-    dist.destroy_process_group()
-    print(f"rank {rank} ok ({mode}, ws={ws})", flush=True)
+def synthetic_batch(batch_size, seed):
+    """SURVEY.md 8(d) synthetic batch (the generator oracle/gen_golden.py and every parity test use)."""
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(batch_size, 1, 28, 28, generator=g)
+    return x, torch.randint(0, 10, (batch_size,), generator=g)
 
 
-def main():
-    mode = sys.argv[1] if len(sys.argv) > 1 else "eager"
-    if mode.startswith("prop"):
-        return property_run(mode)
-    rank, ws = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    # NCCL modes: the launcher pins one GPU per process (CUDA_VISIBLE_DEVICES), like one pod -> device 0.
-    # fused modes: all GPUs stay visible (peer mapping needs distinct device ordinals) -> device = rank.
-    dev = torch.device("cuda", 0 if torch.cuda.device_count() == 1 else rank)
-    torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev)
+def fixture_run(dev, fused, graph):
+    rank, ws = dist.get_rank(), dist.get_world_size()
     gold = load_golden("train_ws2_b64")
-    assert ws == int(gold["meta/world_size"][0])
+    assert ws == int(gold["meta/world_size"][0]), "the reference fixture is a world_size-2 run"
     torch.manual_seed(1 + 7 * rank)  # ranks start different; the DDP constructor must broadcast rank 0
     net = pkg.Net().to(dev)
     if rank == 0:
         torch.manual_seed(1)
         net.load_named({k: v for k, v in pkg.Net().state_dict().items()})
-    model = pkg.DistributedDataParallel(net, fused=mode.startswith("fused"))
-    assert model.fused == mode.startswith("fused"), model.fused_error
+    model = pkg.DistributedDataParallel(net, fused=fused)
+    assert model.fused == fused, model.fused_error
     opt = pkg.SGD(model.parameters(), lr=0.01, momentum=0.5)
-    graph = None
+    g = None
     for s in range(int(gold["meta/nsteps"][0])):
-        x, t = golden_batch(gold, 64, s, rank)
-        if mode.endswith("graph") and s > 0:
-            graph = graph or pkg.StepGraph(model, opt, 64)
-            graph.x.copy_(x)
-            graph.target.copy_(t)
-            loss = graph.replay()
+        x, t = synthetic_batch(64, int(gold[f"step{s}/seed_rank{rank}"][0]))
+        if graph and s > 0:
+            g = g or pkg.StepGraph(model, opt, 64)
+            g.x.copy_(x)
+            g.target.copy_(t)
+            loss = g.replay()
         else:
             loss = model.train_step(x.to(dev), t.to(dev), opt)
         want = float(gold[f"step{s}/loss_rank{rank}"][0])
@@ -99,21 +65,79 @@ def main():
                 golden_tensor_check(gold, f"step{s}/grad", n, (v * (1.0 / ws)).cpu().numpy(), rtol=4 * RTOL)
             for n, v in net.named_views(net.flat_params).items():
                 golden_tensor_check(gold, f"step{s}/param", n, v.cpu().numpy())
-    # both ranks hold identical parameters
-    mine = net.flat_params.clone()
+    mine = net.flat_params.clone()   # both ranks hold identical parameters
     dist.broadcast(mine, src=0)
-    assert torch.equal(mine, net.flat_params)
-    # smoke-dist on the same process group
+    assert torch.equal(mine, net.flat_params), "replicas diverged"
+    model.release_graphs()
+    model.close()
+
+
+def property_run(dev, fused, graph=False, steps=6):
+    rank, ws = dist.get_rank(), dist.get_world_size()
+    torch.manual_seed(1)
+    net = pkg.Net().to(dev)
+    model = pkg.DistributedDataParallel(net, fused=fused)
+    assert model.fused == fused, model.fused_error
+    opt = pkg.SGD(model.parameters(), lr=0.01, momentum=0.5)
+    local = pkg.Net().to(dev)                          # this rank's own gradient, without any exchange
+    losses, g = [], None
+    for s in range(steps):
+        x, t = synthetic_batch(64, 5000 + 31 * s + rank)
+        x, t = x.to(dev), t.to(dev)
+        local.flat_params.copy_(net.flat_params)
+        local.forward_backward(x, t)
+        gathered = [torch.empty_like(local.flat_grads) for _ in range(ws)]
+        dist.all_gather(gathered, local.flat_grads)
+        want = gathered[0].clone()
+        for r in range(1, ws):
+            want += gathered[r]                        # rank order, like the fused kernels
+        if graph and s > 0:
+            g = g or pkg.StepGraph(model, opt, 64)
+            g.x.copy_(x)
+            g.target.copy_(t)
+            losses.append(float(g.replay()))
+        else:
+            losses.append(float(model.train_step(x, t, opt)))
+        if model.fused:
+            assert torch.equal(net.flat_grads, want), f"step {s}: fused sum differs from the rank-ordered sum"
+        else:
+            torch.testing.assert_close(net.flat_grads, want, rtol=1e-5, atol=1e-7)   # NCCL's own summation order
+        ref = net.flat_params.clone()
+        dist.broadcast(ref, src=0)
+        assert torch.equal(ref, net.flat_params), f"step {s}: replicas diverged"
+    lt = torch.tensor([losses[0], losses[-1]], device=dev)
+    dist.all_reduce(lt)
+    assert float(lt[1]) < float(lt[0]), losses
+    model.release_graphs()
+    model.close()
+
+
+def smoke_dist_run(sizes=(4, 431296, 1 << 22), iters=5):
+    rank, ws = dist.get_rank(), dist.get_world_size()
     torch.manual_seed(0)
     inp, results = dist_sendrecv.run()
     if rank == 0:
         assert len(results) == ws - 1 and all(torch.equal(r, torch.mul(inp, inp)) for r in results)
-    rows = dist_sendrecv.allreduce_check(sizes=(4, 431296, 1 << 20), iters=3)
+    rows = dist_sendrecv.allreduce_check(sizes=sizes, iters=iters)
     assert all(r["bit_exact"] for r in rows)
-    model.release_graphs()
+    return rows
+
+
+def main():
+    mode = sys.argv[1] if len(sys.argv) > 1 else "eager"
+    rank = int(os.environ["RANK"])
+    # pinned (CUDA_VISIBLE_DEVICES=<rank>, the one-GPU-per-pod view): device 0; all GPUs visible: device = rank
+    dev = torch.device("cuda", 0 if torch.cuda.device_count() == 1 else rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    if mode.startswith("prop"):
+        property_run(dev, fused=mode.startswith("prop-fused"), graph=mode.endswith("graph"))
+    else:
+        fixture_run(dev, fused=mode.startswith("fused"), graph=mode.endswith("graph"))
+    smoke_dist_run()
     dist.barrier()
     dist.destroy_process_group()
-    print(f"rank {rank} ok ({mode})", flush=True)
+    print(f"rank {rank} ok ({mode}, ws={os.environ['WORLD_SIZE']})", flush=True)
 
 
 if __name__ == "__main__":
