@@ -213,6 +213,293 @@ def run_reference_arm(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def load_compute_peaks():
+    """fp32 FMA and TF32 tensor peaks of this GPU: profiles/r02_peaks_fp32_tf32.json, measured on the B200 box by
+    tools/measure_peaks.py the way MEASURED_PEAKS.json was made; datasheet figures if that file is missing."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_peaks_fp32_tf32.json")) as f:
+            p = json.load(f)
+        return {"fp32_tflops": float(p["fp32_ffma_tflops"]), "tf32_tflops": float(p["tf32_tflops"]),
+                "source": "measured (profiles/r02_peaks_fp32_tf32.json, tools/measure_peaks.py)"}
+    except Exception:
+        return {"fp32_tflops": 80.0, "tf32_tflops": 1100.0, "source": "fallback (B200 datasheet: 80 fp32, 1100 dense TF32)"}
+
+
+def kernel_roofline(name, us, B, peaks, cpeaks, traffic):
+    """Roofline of one kernel launch.  The compute ceiling is the one the kernel's arithmetic can reach: the measured
+    fp32 FMA peak for the SIMT (FFMA2) kernels, the measured TF32 tensor peak / 3 for the tcgen05 3xTF32 kernels
+    (three MMAs per algorithmic product; the conv2 weight gradient issues four), none for pure data movement.  The
+    bound is whichever of compute time and HBM time is longer for the ALGORITHMIC work."""
+    mac, bpi, bpl = KERNEL_WORK.get(name, (0, 0, 0))
+    flops, nbytes, t = 2.0 * mac * B, float(bpi * B + bpl), us * 1e-6
+    tc = "tcgen05" in name
+    cpeak = (cpeaks["tf32_tflops"] / 3.0) if tc else cpeaks["fp32_tflops"]
+    t_c, t_m = flops / (cpeak * 1e12), nbytes / (peaks["hbm_gbs"] * 1e9)
+    if t_c >= t_m and flops > 0:
+        roof = {"bound": "tensor" if tc else "fp32", "achieved": flops / t / 1e12, "peak": cpeak, "unit": "TFLOP/s",
+                "peak_source": cpeaks["source"] + ("; TF32 dense peak / 3 (3xTF32 split)" if tc else "; packed fp32 FMA loop")}
+    else:
+        roof = {"bound": "hbm", "achieved": nbytes / t / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "peak_source": peaks["source"] + " (MEASURED_PEAKS.json copy bandwidth)"}
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    roof.update({"traffic": traffic.get(name), "kernel": name, "kernel_us": us, "algorithmic_flops_per_launch": flops,
+                 "algorithmic_bytes_per_launch": nbytes, "hbm_frac": nbytes / t / 1e9 / peaks["hbm_gbs"],
+                 "compute_frac": (flops / t / 1e12 / cpeak) if flops else 0.0})
+    return roof
+
+
+class Bench:
+    """One model / optimizer / process group; run_config() measures one batch size."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+
+        import pytorch_operator_b200 as pkg
+        self.torch, self.dist, self.pkg, self.args = torch, dist, pkg, args
+        self.rank = int(os.environ.get("RANK", 0))
+        self.world = int(os.environ.get("WORLD_SIZE", 1))
+        local_rank = int(os.environ.get("LOCAL_RANK", self.rank))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a GPU: the CUDA path has no CPU fallback")
+        if self.world != args.gpus:
+            raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={self.world}: launch with torch.distributed.run")
+        ndev = torch.cuda.device_count()
+        self.dev = torch.device("cuda", local_rank % ndev)
+        torch.cuda.set_device(self.dev)
+        if self.world > 1:
+            if os.environ.get("NCCL_DEBUG"):  # keep stdout clean for the single JSON line
+                os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.lib = pkg._cabi.lib()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        self.sampler = ClockSampler(self.dev.index if not vis else int(vis.split(",")[self.dev.index]))
+        self.peaks, self.cpeaks = load_peaks(), load_compute_peaks()
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, ms):
+        if self.world == 1:
+            return ms
+        t = self.torch.tensor([ms], device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t)
+
+    # ---- parity prologue (N > 1): put the multi-GPU checks on the record before anything is timed ----
+    def parity_prologue(self):
+        """tests/ddp_worker.py's checks, in this process group: the reference's ws=2 gloo fixture (N=2), fused sum ==
+        rank-ordered sum bit for bit, replicas bit-identical after every step (eager and CUDA-graph steps), smoke-dist
+        send/recv + all_reduce bit-exact.  Returns the parity block; any failure on any rank ends the run non-zero."""
+        torch, dist = self.torch, self.dist
+        from tests import ddp_worker as dw
+        probe = self.pkg.DistributedDataParallel(self.pkg.Net().to(self.dev))  # which exchange path does this box give?
+        fused = bool(probe.fused)
+        why = probe.fused_error
+        probe.close()
+        out = {"exchange": "fused peer-window kernels" if fused else f"nccl all_reduce ({why})"}
+
+        def run(key, fn):
+            try:
+                fn()
+                ok = 1
+            except Exception as e:  # AssertionError from a check, or a CUDA/NCCL error
+                ok = 0
+                print(f"rank {self.rank}: parity check {key} failed: {e!r}", file=sys.stderr, flush=True)
+            flag = torch.tensor([ok], device=self.dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            out[key] = "pass" if int(flag) == 1 else "FAIL"
+
+        if self.world == 2:
+            run("ws2_fixture", lambda: dw.fixture_run(self.dev, fused=fused, graph=True))
+        else:
+            out["ws2_fixture"] = "n/a (the reference fixture is a world_size-2 run)"
+        run("rank_ordered_sum", lambda: dw.property_run(self.dev, fused=fused, graph=True, steps=5))
+        out["replicas_identical"] = out["rank_ordered_sum"]   # one run checks both after every step
+        run("smoke_dist", lambda: dw.smoke_dist_run(sizes=(4, 431296), iters=3))
+        out["ok"] = all(out[k] == "pass" or out[k].startswith("n/a") for k in ("ws2_fixture", "rank_ordered_sum", "smoke_dist"))
+        return out
+
+    def build_model(self):
+        torch, pkg = self.torch, self.pkg
+        torch.manual_seed(1)
+        self.net = pkg.Net().to(self.dev)
+        self.model = pkg.DistributedDataParallel(self.net) if self.world > 1 else self.net
+        self.opt = pkg.SGD(self.model.parameters(), lr=0.01, momentum=0.5)
+
+    # ---- one workload ----
+    def run_config(self, B, K, W, profile_iters):
+        torch, pkg, lib, dev, world, rank = self.torch, self.pkg, self.lib, self.dev, self.world, self.rank
+        model, net, opt = self.model, self.net, self.opt
+        # synthetic data: packed [x fp32 | target int64] records, one record per batch
+        xb, tb = B * 784 * 4, B * 8
+        rec = xb + tb
+        nring = max(8, min(RING_DEVICE, (256 << 20) // rec))
+        g = torch.Generator(device=dev).manual_seed(1234 + rank)
+        ring = torch.empty(nring, rec, dtype=torch.uint8, device=dev)
+        ring[:, :xb].view(torch.float32).normal_(generator=g)
+        ring[:, xb:].view(torch.int64).copy_(torch.randint(0, 10, (nring, B), generator=g, device=dev))
+        nhost = max(4, min(RING_HOST, (64 << 20) // rec))
+        host_ring = torch.empty(nhost, rec, dtype=torch.uint8).pin_memory()
+        host_ring.copy_(ring[:nhost])
+        static = torch.zeros(rec, dtype=torch.uint8, device=dev)
+        sx = static[:xb].view(torch.float32).view(B, 1, 28, 28)
+        st = static[xb:].view(torch.int64)
+
+        # first step eager (initialises momentum), count kernels per step, capture the graph
+        self.barrier()
+        static.copy_(ring[0])
+        model.train_step(sx, st, opt)
+        torch.cuda.synchronize()
+        c0 = lib.b200mnist_launch_count()
+        model.train_step(sx, st, opt)
+        torch.cuda.synchronize()
+        kernels_per_step = int(lib.b200mnist_launch_count() - c0)
+        graph = pkg.StepGraph(model, opt, B, x=sx, target=st)
+
+        # leg 1: device-resident inputs (value)
+        for i in range(W):
+            static.copy_(ring[i % nring], non_blocking=True)
+            graph.replay()
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_start = time.time()
+        e0.record()
+        for i in range(K):
+            static.copy_(ring[i % nring], non_blocking=True)
+            graph.replay()
+        e1.record()
+        self.barrier()
+        t_end = time.time()
+        ms_total = self.max_over_ranks(e0.elapsed_time(e1))
+        clocks = ClockSampler.summarise(self.sampler.window(t_start, t_end))
+        loss_final = float(graph.loss)
+
+        # leg 2: end to end from pinned host memory, loss read back every step.  Public API:
+        # StepPipeline.submit(pinned record) = H2D on a copy stream (double-buffered), graph replay, the loss stored
+        # into pinned host memory by the step's last kernel -- all inside the timed region, every step.
+        pipe = pkg.StepPipeline(model, opt, B)
+        for i in range(W):
+            pipe.submit(host_ring[i % nhost])
+        pipe.drain()
+        self.barrier()
+        t2_start = time.time()
+        e0.record()
+        for i in range(K):
+            pipe.submit(host_ring[i % nhost])
+        e1.record()
+        pipe.drain()
+        self.barrier()
+        t2_end = time.time()
+        ms_e2e = self.max_over_ranks(e0.elapsed_time(e1))
+        clocks_e2e = ClockSampler.summarise(self.sampler.window(t2_start, t2_end))
+        if not bool(torch.isfinite(pipe.loss_host).all()):
+            raise SystemExit("non-finite loss in the timed region")
+
+        # fused exchange: where one step's time goes (CUDA events on both streams of eager fused steps, launches
+        # queued behind a delay kernel so host gaps do not count)
+        timeline = None
+        if world > 1 and getattr(model, "fused", False):
+            acc, n_tl = {}, 20
+            stream = torch.cuda.current_stream().cuda_stream
+            for it in range(n_tl + 3):
+                static.copy_(ring[it % nring], non_blocking=True)
+                self.barrier()
+                model.timeline = {}
+                lib.b200mnist_delay(stream, 300)
+                model.train_step(sx, st, opt)
+                torch.cuda.synchronize()
+                ev = model.timeline
+                model.timeline = None
+                if it >= 3:
+                    for k in ("phase1_end", "fc1_exchange_end", "phase2_end", "rest_exchange_end"):
+                        acc[k] = acc.get(k, 0.0) + ev["start"].elapsed_time(ev[k]) * 1e3 / n_tl
+            timeline = {k: round(self.max_over_ranks(v), 2) for k, v in acc.items()}
+
+        net.release_graphs()
+        del graph, pipe
+        out = {"B": B, "K": K, "W": W, "rec": rec, "nring": nring, "ms_total": ms_total, "ms_e2e": ms_e2e,
+               "kernels_per_step": kernels_per_step, "clocks": clocks, "clocks_e2e": clocks_e2e,
+               "loss_final": loss_final, "timeline": timeline}
+        if rank != 0:
+            return out
+
+        # per-kernel durations (rank 0): CUDA events on the launching stream after every kernel of this rank's step
+        # (the collective is timed separately).  Event-to-event times carry the cost of the event itself and lose
+        # the programmatic-dependent-launch overlap, so they are scaled to add up to the same eager step timed with
+        # one event pair around it (both runs queue behind a delay kernel: no host gaps).
+        import ctypes
+        names_buf = (ctypes.c_char_p * 64)()
+        ms_buf = (ctypes.c_float * 64)()
+        stream = torch.cuda.current_stream().cuda_stream
+        sums, counts = {}, {}
+        saved = [t.clone() for t in (net.flat_params, net.flat_grads, net.flat_momentum)]
+        ddp_saved = net._ddp
+        object.__setattr__(net, "_ddp", None)
+        plain_us = 0.0
+        for it in range(profile_iters + 3):
+            static.copy_(ring[it % nring], non_blocking=True)
+            pkg._cabi.check(lib.b200mnist_profile_begin(stream, 400), "profile_begin")
+            net.train_step(sx, st, opt)
+            n = lib.b200mnist_profile_end(ms_buf, names_buf, 64, stream)
+            if n < 0:
+                raise SystemExit("profile_end failed: " + pkg._cabi.last_error())
+            lib.b200mnist_delay(stream, 400)
+            e0.record()
+            net.train_step(sx, st, opt)
+            e1.record()
+            torch.cuda.synchronize()
+            if it < 3:
+                continue
+            plain_us += e0.elapsed_time(e1) * 1e3 / profile_iters
+            for i in range(n):
+                nm = names_buf[i].decode()
+                sums[nm] = sums.get(nm, 0.0) + ms_buf[i]
+                counts[nm] = counts.get(nm, 0) + 1
+        object.__setattr__(net, "_ddp", ddp_saved)
+        for t, sv in zip((net.flat_params, net.flat_grads, net.flat_momentum), saved):
+            t.copy_(sv)
+        torch.cuda.synchronize()
+        raw_us = {k: 1e3 * sums[k] / counts[k] for k in sums}
+        raw_sum = sum(raw_us.values())
+        scale = min(1.0, plain_us / raw_sum) if raw_sum > 0 else 1.0
+        out.update({"kern_us": {k: v * scale for k, v in raw_us.items()}, "kern_us_raw_sum": raw_sum,
+                    "eager_step_us": plain_us, "event_scale": scale})
+        return out
+
+    def report(self, r):
+        """JSON fields of one measured config."""
+        B, K, world = r["B"], r["K"], self.world
+        step_us = 1e3 * r["ms_total"] / K
+        kern_us = r["kern_us"]
+        top = max(kern_us, key=kern_us.get)
+        traffic = load_traffic(B)
+        roof = kernel_roofline(top, kern_us[top], B, self.peaks, self.cpeaks, traffic)
+        roof["note"] = ("dominant kernel of the step by duration; kernel_us = CUDA-event time of the kernel on its launching "
+                        "stream, scaled so that the kernels add up to the eager step timed with one event pair")
+        step_flops, step_bytes = FLOPS_PER_IMAGE * B, HBM_BYTES_PER_IMAGE * B + 8 * PARAM_BYTES
+        t = step_us * 1e-6
+        simt_share = sum(v for k, v in kern_us.items() if "tcgen05" not in k) / max(sum(kern_us.values()), 1e-9)
+        return {
+            "ms_per_step": r["ms_total"] / K, "img_s": world * B * K / (r["ms_total"] * 1e-3),
+            "e2e": {"value": world * B * K / (r["ms_e2e"] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": r["rec"],
+                    "d2h_bytes_per_step": 4, "ms_per_step": r["ms_e2e"] / K},
+            "kernels_per_step": r["kernels_per_step"], "roofline": roof,
+            "step_roofline": {"flops_per_step": step_flops, "hbm_bytes_per_step": step_bytes,
+                              "tflops": step_flops / t / 1e12, "hbm_gbs": step_bytes / t / 1e9,
+                              "frac_of_hbm_peak": step_bytes / t / 1e9 / self.peaks["hbm_gbs"],
+                              "frac_of_fp32_peak": step_flops / t / 1e12 / self.cpeaks["fp32_tflops"],
+                              "frac_of_tf32_peak_over_3": step_flops / t / 1e12 / (self.cpeaks["tf32_tflops"] / 3.0),
+                              "simt_share_of_kernel_time": simt_share},
+            "kernel_us": {k: round(v, 3) for k, v in sorted(kern_us.items(), key=lambda kv: -kv[1])},
+            "kernel_us_sum": round(sum(kern_us.values()), 3), "kernel_us_raw_event_sum": round(r["kern_us_raw_sum"], 3),
+            "eager_step_us": round(r["eager_step_us"], 3), "clocks": r["clocks"], "clocks_e2e": r["clocks_e2e"],
+            "final_loss": r["loss_final"], "exchange_timeline_us": r["timeline"],
+        }
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -223,235 +510,108 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ref-budget", type=float, default=20.0, help="--impl reference: seconds of timed CPU work")
     ap.add_argument("--profile-iters", type=int, default=30)
+    ap.add_argument("--no-config5", action="store_true", help="skip the batch-4096 leg (BASELINE configs[4])")
+    ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity prologue (N > 1)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
-    world = int(os.environ.get("WORLD_SIZE", 1))
-    local_rank = int(os.environ.get("LOCAL_RANK", rank))
 
     if args.impl == "reference":
         run_reference_arm(args, rank)
         return
 
-    import torch
-    import torch.distributed as dist
+    b = Bench(args)
+    torch, dist, world = b.torch, b.dist, b.world
+    W, K, B = max(args.warmup, 3), args.steps, args.batch
 
-    import pytorch_operator_b200 as pkg
-
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a GPU: the CUDA path has no CPU fallback")
-    if world != args.gpus:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
-    W = max(args.warmup, 3)
-    K = args.steps
-    B = args.batch
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        if os.environ.get("NCCL_DEBUG"):  # keep stdout clean for the single JSON line
-            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
-    lib = pkg._cabi.lib()
-
-    torch.manual_seed(1)
-    model = pkg.Net().to(dev)
-    net = model
-    if world > 1:
-        model = pkg.DistributedDataParallel(model)
-    opt = pkg.SGD(model.parameters(), lr=0.01, momentum=0.5)
-
-    # ---- synthetic data: packed [x fp32 | target int64] records, one record per batch ----
-    xb, tb = B * 784 * 4, B * 8
-    rec = xb + tb
-    nring = max(8, min(RING_DEVICE, (256 << 20) // rec))
-    g = torch.Generator(device=dev).manual_seed(1234 + rank)
-    ring = torch.empty(nring, rec, dtype=torch.uint8, device=dev)
-    ring[:, :xb].view(torch.float32).normal_(generator=g)
-    ring[:, xb:].view(torch.int64).copy_(torch.randint(0, 10, (nring, B), generator=g, device=dev))
-    nhost = max(4, min(RING_HOST, (64 << 20) // rec))
-    host_ring = torch.empty(nhost, rec, dtype=torch.uint8).pin_memory()
-    host_ring.copy_(ring[:nhost])
-    static = torch.zeros(rec, dtype=torch.uint8, device=dev)
-    sx = static[:xb].view(torch.float32).view(B, 1, 28, 28)
-    st = static[xb:].view(torch.int64)
-
-    # ---- first step eager (initialises momentum), count kernels per step, capture the graph ----
-    static.copy_(ring[0])
-    model.train_step(sx, st, opt)
-    torch.cuda.synchronize()
-    c0 = lib.b200mnist_launch_count()
-    model.train_step(sx, st, opt)
-    torch.cuda.synchronize()
-    kernels_per_step = int(lib.b200mnist_launch_count() - c0)
-    graph = pkg.StepGraph(model, opt, B, x=sx, target=st)
-
-    def barrier():
-        if world > 1:
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = b.parity_prologue()
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "value": None, "n_gpus": world, "parity": parity,
+                                  "error": "multi-GPU parity check failed; nothing was timed"}), flush=True)
             dist.barrier()
-        torch.cuda.synchronize()
+            dist.destroy_process_group()
+            sys.exit(1)
 
-    def max_over_ranks(ms):
-        if world == 1:
-            return ms
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t)
+    b.build_model()
+    main_r = b.run_config(B, K, W, args.profile_iters)
+    c5 = None
+    if not args.no_config5 and B != 4096:
+        # BASELINE configs[4]: 4096 images per rank, the tcgen05 kernels (>= 10 warm-up + >= 100 steps)
+        c5 = b.run_config(4096, max(100, min(K, 300)), max(10, min(W, 30)), min(args.profile_iters, 10))
 
-    sampler = ClockSampler(torch.cuda.current_device() if os.environ.get("CUDA_VISIBLE_DEVICES") is None
-                           else int(os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local_rank]))
-
-    # ---- leg 1: device-resident inputs (value) ----
-    for i in range(W):
-        static.copy_(ring[i % nring], non_blocking=True)
-        graph.replay()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_start = time.time()
-    e0.record()
-    for i in range(K):
-        static.copy_(ring[i % nring], non_blocking=True)
-        graph.replay()
-    e1.record()
-    barrier()
-    t_end = time.time()
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
-    clocks = ClockSampler.summarise(sampler.window(t_start, t_end))
-    loss_final = float(graph.loss)
-
-    # ---- leg 2: end to end from pinned host memory, loss read back every step ----
-    # public API: StepPipeline.submit(pinned record) = H2D on a copy stream (double-buffered), graph replay,
-    # D2H copy node of the loss into pinned host memory -- all inside the timed region, every step.
-    pipe = pkg.StepPipeline(model, opt, B)
-    for i in range(W):
-        pipe.submit(host_ring[i % nhost])
-    pipe.drain()
-    barrier()
-    t2_start = time.time()
-    e0.record()
-    for i in range(K):
-        pipe.submit(host_ring[i % nhost])
-    e1.record()
-    pipe.drain()
-    barrier()
-    t2_end = time.time()
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
-    clocks_e2e = ClockSampler.summarise(sampler.window(t2_start, t2_end))
-    sampler.stop()
-    if not bool(torch.isfinite(pipe.loss_host).all()):
-        raise SystemExit("non-finite loss in the timed region")
-
-    # ---- gradient all_reduce bus bandwidth (the second half of BASELINE.json's metric), all ranks ----
+    # gradient all_reduce bus bandwidth (the second half of BASELINE.json's metric), all ranks
     busbw = None
     if world > 1:
-        buf = torch.zeros(net.flat_grads.numel(), dtype=torch.float32, device=dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        buf = torch.zeros(b.net.flat_grads.numel(), dtype=torch.float32, device=b.dev)
         for _ in range(5):
             dist.all_reduce(buf)
-        barrier()
+        b.barrier()
         e0.record()
         for _ in range(50):
             dist.all_reduce(buf)
         e1.record()
         torch.cuda.synchronize()
-        ar_ms = max_over_ranks(e0.elapsed_time(e1) / 50)
+        ar_ms = b.max_over_ranks(e0.elapsed_time(e1) / 50)
         nbytes_ar = buf.numel() * 4
         busbw = {"bytes": nbytes_ar, "nccl_time_us": ar_ms * 1e3,
                  "nccl_busbw_GBps": nbytes_ar / (ar_ms * 1e-3) * 2 * (world - 1) / world / 1e9}
+    b.sampler.stop()
+    fused = bool(getattr(b.model, "fused", False))
 
-    if rank != 0:
+    def teardown():
         if world > 1:
-            net.release_graphs()  # a graph holding NCCL kernels would make destroy_process_group() block
+            b.net.release_graphs()  # a graph holding NCCL kernels would make destroy_process_group() block
+            b.model.close()
             dist.barrier()
             dist.destroy_process_group()
-        return
 
-    # ---- per-kernel durations, CUDA events on the launching stream (rank 0) ----
-    import ctypes
-    names_buf = (ctypes.c_char_p * 64)()
-    ms_buf = (ctypes.c_float * 64)()
-    stream = torch.cuda.current_stream().cuda_stream
-    sums, counts = {}, {}
-    pnet, popt = net, opt
-    saved = [t.clone() for t in (pnet.flat_params, pnet.flat_grads, pnet.flat_momentum)]
-    ddp_saved = pnet._ddp
-    object.__setattr__(pnet, "_ddp", None)  # time this rank's kernels; the collective is timed separately
-    for it in range(args.profile_iters + 3):
-        static.copy_(ring[it % nring], non_blocking=True)
-        pkg._cabi.check(lib.b200mnist_profile_begin(stream, 400), "profile_begin")
-        pnet.train_step(sx, st, popt)
-        n = lib.b200mnist_profile_end(ms_buf, names_buf, 64, stream)
-        if n < 0:
-            raise SystemExit("profile_end failed: " + pkg._cabi.last_error())
-        if it < 3:
-            continue
-        for i in range(n):
-            nm = names_buf[i].decode()
-            sums[nm] = sums.get(nm, 0.0) + ms_buf[i]
-            counts[nm] = counts.get(nm, 0) + 1
-    object.__setattr__(pnet, "_ddp", ddp_saved)
-    for t, sv in zip((pnet.flat_params, pnet.flat_grads, pnet.flat_momentum), saved):
-        t.copy_(sv)
-    kern_us = {k: 1e3 * sums[k] / counts[k] for k in sums}
-    peaks = load_peaks()
-    top = max(kern_us, key=kern_us.get)
-    mac, bpi, bpl = KERNEL_WORK.get(top, (0, 0, 0))
-    flops = 2.0 * mac * B
-    nbytes = float(bpi * B + bpl)
-    t_top = kern_us[top] * 1e-6
-    t_tensor, t_hbm = flops / (peaks["bf16_tflops"] * 1e12), nbytes / (peaks["hbm_gbs"] * 1e9)
-    if t_tensor >= t_hbm:
-        roof = {"bound": "tensor", "achieved": flops / t_top / 1e12, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s"}
-    else:
-        roof = {"bound": "hbm", "achieved": nbytes / t_top / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s"}
-    roof["frac"] = roof["achieved"] / roof["peak"]
-    roof.update({"traffic": load_traffic(B).get(top), "kernel": top, "kernel_us": kern_us[top], "peak_source": peaks["source"] +
-                 " (MEASURED_PEAKS.json burst bf16 / copy bandwidth)", "algorithmic_flops_per_launch": flops,
-                 "algorithmic_bytes_per_launch": nbytes,
-                 "note": ("tcgen05 3xTF32 kernel: algorithmic (fp32-equivalent) FLOPs of the dense product against the "
-                          "bf16 tensor peak; the MMAs issued are 2-4x that (hi/lo products) at TF32 rate (half of bf16)"
-                          if "tcgen05" in top else
-                          "fp32 SIMT (FFMA2) kernel -- 1e-5 parity rules out single-pass TF32/bf16 MMA; at this batch the "
-                          "kernel is latency/occupancy bound (see profiles/), so both roofline fractions are low by construction")})
-    step_us = 1e3 * ms_total / K
-    step_flops, step_bytes = FLOPS_PER_IMAGE * B, HBM_BYTES_PER_IMAGE * B + 8 * PARAM_BYTES
+    if rank != 0:
+        teardown()
+        return
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         cpu = cpu_reference_run(B, 2000, 20, budget_s=12.0)
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
 
+    m = b.report(main_r)
     line = {
-        "metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
-        "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": METRIC, "value": m["img_s"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"examples/mnist Net DDP train step (BASELINE configs[{1 if world == 1 else 2}]), "
                                f"per-rank batch {B}, synthetic 1x28x28", "global_batch": world * B,
-                   "parallelism": f"dp{world}", "l2": f"inputs cycle through {nring} distinct device-resident batches "
-                                                      f"({nring * rec / 1e6:.0f} MB > 126 MB L2)",
+                   "parallelism": f"dp{world}", "l2": f"inputs cycle through {main_r['nring']} distinct device-resident "
+                                                      f"batches ({main_r['nring'] * main_r['rec'] / 1e6:.0f} MB > 126 MB L2)",
                    "cuda_graph": True, "lr": 0.01, "momentum": 0.5},
-        "e2e": {"value": world * B * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": rec,
-                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K,
-                "how": "StepPipeline.submit(pinned record): H2D on a copy stream into the idle one of two static buffers, graph replay, the loss stored by the last kernel straight into pinned host memory (zero-copy D2H) -- every step"},
-        "gpu_launches": kernels_per_step * K,
-        "kernels_per_step": kernels_per_step,
-        "clocks": clocks, "clocks_e2e": clocks_e2e,
-        "roofline": roof,
-        "step_roofline": {"flops_per_step": step_flops, "hbm_bytes_per_step": step_bytes,
-                          "tflops": step_flops / (step_us * 1e-6) / 1e12,
-                          "hbm_gbs": step_bytes / (step_us * 1e-6) / 1e9,
-                          "frac_of_bf16_peak": step_flops / (step_us * 1e-6) / 1e12 / peaks["bf16_tflops"],
-                          "frac_of_hbm_peak": step_bytes / (step_us * 1e-6) / 1e9 / peaks["hbm_gbs"]},
-        "kernel_us": {k: round(v, 3) for k, v in sorted(kern_us.items(), key=lambda kv: -kv[1])},
-        "kernel_us_sum": round(sum(kern_us.values()), 3),
-        "ddp_exchange": (None if world == 1 else ("fused peer-memory all-reduce+SGD kernel (NVLink P2P, symmetric memory)"
-                                                  if model.fused else "NCCL all_reduce + SGD kernel")),
-        "grad_allreduce": busbw,
-        "cpu_baseline": cpu,
-        "final_loss": loss_final,
+        "e2e": dict(m["e2e"], how="StepPipeline.submit(pinned record): H2D on a copy stream into the idle one of two "
+                                  "static buffers, graph replay, the loss stored by the last kernel straight into pinned "
+                                  "host memory (zero-copy D2H) -- every step.  The value leg pays a device-to-device "
+                                  "copy of each batch on the compute stream that this leg's copy stream overlaps, so e2e "
+                                  "can come out slightly above value."),
+        "gpu_launches": m["kernels_per_step"] * K, "kernels_per_step": m["kernels_per_step"],
+        "clocks": m["clocks"], "clocks_e2e": m["clocks_e2e"], "roofline": m["roofline"],
+        "step_roofline": m["step_roofline"], "kernel_us": m["kernel_us"], "kernel_us_sum": m["kernel_us_sum"],
+        "kernel_us_raw_event_sum": m["kernel_us_raw_event_sum"], "eager_step_us": m["eager_step_us"],
+        "ddp_exchange": (None if world == 1 else ("fused peer-window kernels over NVLink (CUDA IPC): two-shot fc1 "
+                                                  "slice reduce+SGD+push beside the conv backward, one-shot remainder"
+                                                  if fused else "NCCL all_reduce + SGD kernel")),
+        "exchange_timeline_us": m["exchange_timeline_us"], "grad_allreduce": busbw, "parity": parity,
+        "cpu_baseline": cpu, "final_loss": m["final_loss"],
     }
+    if c5 is not None:
+        c = b.report(c5)
+        line["config5"] = {"workload": "examples/mnist Net DDP train step (BASELINE configs[4]), per-rank batch 4096, "
+                                       "tcgen05 conv2 / fc1 kernels", "global_batch": world * 4096, "steps": c5["K"],
+                           "warmup": c5["W"], **{k: c[k] for k in ("ms_per_step", "img_s", "e2e", "kernels_per_step",
+                                                                    "roofline", "step_roofline", "kernel_us",
+                                                                    "kernel_us_sum", "eager_step_us", "clocks",
+                                                                    "final_loss", "exchange_timeline_us")}}
     print(json.dumps(line), flush=True)
-    if world > 1:
-        net.release_graphs()
-        dist.barrier()
-        dist.destroy_process_group()
+    teardown()
 
 
 if __name__ == "__main__":

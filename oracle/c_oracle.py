@@ -52,15 +52,30 @@ def forward(params, x):
     return act
 
 
-def loss_and_grads(params, x, target, idx_override=None):
+def loss_and_grads(params, x, target, idx_override=None, mask_override=None):
     """Returns (loss, logp, grads dict) for one batch; the C analogue of
     mnist_oracle.loss_and_grads.  ``idx_override=(i1, i2)`` teacher-forces the max-pool
-    arg-max maps used by the backward (see mnist_oracle.pool_tie_gap)."""
+    arg-max maps used by the backward (see mnist_oracle.pool_tie_gap).
+    ``mask_override=(p1, p2, h)`` (the activations another implementation saved) teacher-forces the
+    three ReLU masks of the backward as well: wherever that implementation and this one disagree on
+    ``activation > 0`` the other one's value is taken; a fourth return value then reports, per layer,
+    how many masks were forced and the largest activation magnitude among them (a legitimate
+    disagreement is one within rounding of the kink, i.e. that magnitude is ~1e-6)."""
     B = int(x.shape[0])
     act = forward(params, x)
     if idx_override is not None:
         act["i1"] = np.ascontiguousarray(idx_override[0], dtype=np.uint8).reshape(act["i1"].shape)
         act["i2"] = np.ascontiguousarray(idx_override[1], dtype=np.uint8).reshape(act["i2"].shape)
+    forced = None
+    if mask_override is not None:
+        forced = {}
+        for key, other in zip(("p1", "p2", "h"), mask_override):
+            mine = act[key]
+            other = np.asarray(other, dtype=np.float32).reshape(mine.shape)
+            diff = (mine > 0) != (other > 0)
+            mag = max(float(np.abs(mine[diff]).max(initial=0.0)), float(np.abs(other[diff]).max(initial=0.0)))
+            forced[key] = (int(diff.sum()), mag)
+            mine[diff] = other[diff]
     t = np.ascontiguousarray(target, dtype=np.int64)
     vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)
     loss = lib().lenet_nll_mean(vp(act["logp"]), vp(t), ctypes.c_int(B))
@@ -69,6 +84,8 @@ def loss_and_grads(params, x, target, idx_override=None):
     lib().lenet_backward(keep["conv2.weight"][1], keep["fc1.weight"][1], keep["fc2.weight"][1],
                          vp(act["x"]), vp(t), ctypes.c_int(B), vp(act["p1"]), vp(act["i1"]), vp(act["p2"]),
                          vp(act["i2"]), vp(act["h"]), vp(act["logp"]), *[vp(grads[n]) for n in NAMES])
+    if forced is not None:
+        return float(loss), act["logp"], grads, forced
     return float(loss), act["logp"], grads
 
 
