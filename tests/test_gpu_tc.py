@@ -28,7 +28,7 @@ def test_fc1_tensor_core_path_matches_fp64(B):
     # and against the fp32 SIMT kernel (same tolerance)
     out2 = torch.empty(B, 500, device=DEV)
     sc = torch.zeros(int(L.b200mnist_fc1_scratch_bytes(B)), dtype=torch.uint8, device=DEV)
-    if B < 1024:  # b200mnist_fc1_relu_fwd itself switches to the tensor-core path from 1024 up
+    if B < 384:  # b200mnist_fc1_relu_fwd itself switches to the tensor-core path from 384 up (kTcMinBatch)
         _cabi.check(L.b200mnist_fc1_relu_fwd(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), out2.data_ptr(), B,
                                              sc.data_ptr(), torch.cuda.current_stream().cuda_stream), "fc1 simt")
         assert_close(out.cpu().numpy(), out2.cpu().numpy(), rtol=RTOL, what="tcgen05 vs SIMT")
@@ -62,7 +62,7 @@ def test_fc_backward_tensor_core_path_matches_fp64(B):
         assert_close(out[k].cpu().numpy(), ref[k].numpy(), rtol=RTOL, what=f"{k} (B={B})")
 
 
-@pytest.mark.parametrize("B", [1, 2, 63, 64, 300, 1000])
+@pytest.mark.parametrize("B", [1, 2, 63, 64, 300, 1000, 4096])
 def test_conv2_implicit_gemm_tensor_core_path_matches_oracle(B):
     """conv2 + ReLU + pool as a tcgen05 shifted-window implicit GEMM against float64, and its arg-max map against
     the fp32 SIMT kernel wherever the window maximum is not a near-tie.  B=300 and 1000 make the persistent CTAs
@@ -87,7 +87,7 @@ def test_conv2_implicit_gemm_tensor_core_path_matches_oracle(B):
                        *extra, torch.cuda.current_stream().cuda_stream), name)
         torch.cuda.synchronize()
         outs[name] = (out.cpu(), idx.cpu())
-    c = F.relu(F.conv2d(p1.double(), w.double(), b.double()))
+    c = F.relu(F.conv2d(p1.to(DEV).double(), w.to(DEV).double(), b.to(DEV).double())).cpu()   # float64 on the GPU
     ref = F.max_pool2d(c, 2, 2)
     assert_close(outs["tc"][0].numpy(), ref.numpy(), rtol=RTOL, what=f"p2 tcgen05 B={B}")
     win = c.unfold(2, 2, 2).unfold(3, 2, 2).reshape(B, 50, 4, 4, 4)
@@ -97,12 +97,14 @@ def test_conv2_implicit_gemm_tensor_core_path_matches_oracle(B):
     assert np.array_equal(outs["tc"][1].numpy()[clear.numpy()], outs["simt"][1].numpy()[clear.numpy()])
 
 
-@pytest.mark.parametrize("B", [1, 2, 3, 64, 75, 300])
+@pytest.mark.parametrize("B", [1, 2, 3, 64, 75, 300, 4096])
 def test_conv2_backward_tensor_core_paths_match_float64(B, monkeypatch):
     """conv2 backward with the data gradient (GEMM + col2im epilogue) and/or the weight gradient (one MMA per
     hi/lo quartet, fp32 folds every 8 images) on tcgen05, and with the fp32 SIMT kernel: all four combinations
     against float64 autograd formulas on the same arg-max map.  Odd B leaves half an image pair empty, B=75/300
-    make the persistent CTAs walk several tiles (double-buffered operands, patches, accumulators, drains)."""
+    make the persistent CTAs walk several tiles (double-buffered operands, patches, accumulators, drains); B=4096
+    (BASELINE configs[4]) runs the weight gradient's 29 slices x ~141 images with a TMEM -> shared-memory fold every
+    8 images and ~55 data-gradient tiles per CTA."""
     import torch.nn.functional as F
     from oracle import mnist_oracle as mo
     from pytorch_operator_b200 import _cabi

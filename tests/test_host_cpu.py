@@ -181,3 +181,32 @@ def test_reference_arm_survives_a_torchrun_environment():
     r1 = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                         env=dict(env, RANK="1", LOCAL_RANK="1"), capture_output=True, text=True, timeout=60)
     assert r1.returncode == 0 and r1.stdout.strip() == ""
+
+
+@pytest.mark.parametrize("name,module,args", [
+    ("pytorch_job_mnist_b200_nccl.yaml", "pytorch_operator_b200.mnist", ["--backend", "nccl"]),
+    ("pytorch_job_smoke_dist_b200.yaml", "pytorch_operator_b200.dist_sendrecv", []),
+])
+def test_pytorchjob_manifests_follow_the_operator_contract(name, module, args):
+    """The B200 manifests against what the operator requires of a PyTorchJob: container named "pytorch"
+    (pkg/apis/pytorch/v1/constants.go:29, validation.go:58-62), port name "pytorchjob-port" = 23456
+    (constants.go:27,31), exactly one Master (manifests/crd.yaml:28-33), restartPolicy OnFailure (constants.go:33),
+    one GPU per replica as in examples/mnist/v1/pytorch_job_mnist_nccl.yaml -- and 1 + 7 replicas for one 8-GPU node,
+    whose env the launcher reproduces."""
+    import yaml
+    with open(os.path.join(ROOT, "manifests", name)) as f:
+        job = yaml.safe_load(f)
+    assert job["apiVersion"] == "kubeflow.org/v1" and job["kind"] == "PyTorchJob"
+    specs = job["spec"]["pytorchReplicaSpecs"]
+    assert set(specs) == {"Master", "Worker"} and specs["Master"]["replicas"] == 1 and specs["Worker"]["replicas"] == 7
+    for rs in specs.values():
+        assert rs["restartPolicy"] == "OnFailure"
+        (c,) = rs["template"]["spec"]["containers"]
+        assert c["name"] == "pytorch" and c["command"] == ["python", "-m", module] and c["args"] == args
+        assert c["ports"] == [{"name": "pytorchjob-port", "containerPort": launcher.DEFAULT_PORT}]
+        assert c["resources"]["limits"]["nvidia.com/gpu"] == 1
+    total = specs["Master"]["replicas"] + specs["Worker"]["replicas"]
+    envs = [launcher.cluster_spec(job["metadata"]["name"], 7, "master", 0)] + \
+           [launcher.cluster_spec(job["metadata"]["name"], 7, "worker", i) for i in range(7)]
+    assert [e["RANK"] for e in envs] == [str(r) for r in range(total)] and {e["WORLD_SIZE"] for e in envs} == {"8"}
+    assert envs[1]["MASTER_ADDR"] == job["metadata"]["name"] + "-master-0" and envs[0]["MASTER_ADDR"] == "localhost"

@@ -120,3 +120,25 @@ def test_kink_and_tie_gaps_select_usable_batches():
                                                                     pp["conv2.bias"].double()), 2, 2)
     pp["conv2.bias"][0] -= pre[0, 0, 0, 0].float()
     assert mo.relu_kink_gap(pp, x)[0] < 1e-6
+
+
+def test_c_oracle_mask_override_is_neutral_on_its_own_activations_and_flips_on_request():
+    """c_oracle.loss_and_grads(mask_override=...) (used by the large-batch GPU parity test): forcing the oracle's own
+    activations changes nothing; forcing one dead fc1 unit alive (a tiny positive value) opens exactly that gradient
+    path and is reported."""
+    import numpy as np
+    from oracle import c_oracle
+    params = {k: v.numpy() for k, v in mo.init_params(1).items()}
+    x, t = mo.synthetic_batch(3, 17)
+    act = c_oracle.forward(params, x.numpy())
+    base = c_oracle.loss_and_grads(params, x.numpy(), t.numpy())
+    same = c_oracle.loss_and_grads(params, x.numpy(), t.numpy(), mask_override=(act["p1"], act["p2"], act["h"]))
+    assert same[3] == {"p1": (0, 0.0), "p2": (0, 0.0), "h": (0, 0.0)}
+    assert all(np.array_equal(base[2][k], same[2][k]) for k in base[2])
+    h = act["h"].copy()
+    dead = np.argwhere(h == 0)[0]
+    h[tuple(dead)] = 1e-6
+    flipped = c_oracle.loss_and_grads(params, x.numpy(), t.numpy(), mask_override=(act["p1"], act["p2"], h))
+    assert flipped[3]["h"][0] == 1 and abs(flipped[3]["h"][1] - 1e-6) < 1e-12
+    assert not np.array_equal(base[2]["fc1.bias"], flipped[2]["fc1.bias"])
+    assert np.array_equal(base[2]["fc2.bias"], flipped[2]["fc2.bias"])
