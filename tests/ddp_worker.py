@@ -82,7 +82,9 @@ def property_run(dev, fused, graph=False, steps=6):
     local = pkg.Net().to(dev)                          # this rank's own gradient, without any exchange
     losses, g = [], None
     for s in range(steps):
-        x, t = synthetic_batch(64, 5000 + 31 * s + rank)
+        # one batch per rank, repeated: the gradients still change every step (the parameters move), and the
+        # loss on it must go down -- on fresh random-label batches it would only wander around ln(10)
+        x, t = synthetic_batch(64, 5000 + rank)
         x, t = x.to(dev), t.to(dev)
         local.flat_params.copy_(net.flat_params)
         local.forward_backward(x, t)
