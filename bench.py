@@ -398,25 +398,12 @@ class Bench:
         if not bool(torch.isfinite(pipe.loss_host).all()):
             raise SystemExit("non-finite loss in the timed region")
 
-        # fused exchange: where one step's time goes (CUDA events on both streams of eager fused steps, launches
-        # queued behind a delay kernel so host gaps do not count)
+        # fused exchange: where the exchange sat inside the LAST timed step (GPU globaltimer stamps its kernels leave
+        # in the flag page; microseconds after the exchange CTAs started), max over ranks
         timeline = None
         if world > 1 and getattr(model, "fused", False):
-            acc, n_tl = {}, 20
-            stream = torch.cuda.current_stream().cuda_stream
-            for it in range(n_tl + 3):
-                static.copy_(ring[it % nring], non_blocking=True)
-                self.barrier()
-                model.timeline = {}
-                lib.b200mnist_delay(stream, 300)
-                model.train_step(sx, st, opt)
-                torch.cuda.synchronize()
-                ev = model.timeline
-                model.timeline = None
-                if it >= 3:
-                    for k in ("phase1_end", "fc1_exchange_end", "phase2_end", "rest_exchange_end"):
-                        acc[k] = acc.get(k, 0.0) + ev["start"].elapsed_time(ev[k]) * 1e3 / n_tl
-            timeline = {k: round(self.max_over_ranks(v), 2) for k, v in acc.items()}
+            tel = model.exchange_telemetry()
+            timeline = {k: round(self.max_over_ranks(v), 2) for k, v in tel.items()}
 
         net.release_graphs()
         del graph, pipe
@@ -596,8 +583,9 @@ def main():
         "clocks": m["clocks"], "clocks_e2e": m["clocks_e2e"], "roofline": m["roofline"],
         "step_roofline": m["step_roofline"], "kernel_us": m["kernel_us"], "kernel_us_sum": m["kernel_us_sum"],
         "kernel_us_raw_event_sum": m["kernel_us_raw_event_sum"], "eager_step_us": m["eager_step_us"],
-        "ddp_exchange": (None if world == 1 else ("fused peer-window kernels over NVLink (CUDA IPC): two-shot fc1 "
-                                                  "slice reduce+SGD+push beside the conv backward, one-shot remainder"
+        "ddp_exchange": (None if world == 1 else ("fused into the step's kernels over NVLink peer windows (CUDA IPC): "
+                                                  "two-shot fc1 slice reduce+SGD+push by extra CTAs of the conv1 "
+                                                  "weight-gradient launch, remainder pushed + summed by the last kernel"
                                                   if fused else "NCCL all_reduce + SGD kernel")),
         "exchange_timeline_us": m["exchange_timeline_us"], "grad_allreduce": busbw, "parity": parity,
         "cpu_baseline": cpu, "final_loss": m["final_loss"],

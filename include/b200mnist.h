@@ -95,8 +95,9 @@ int b200mnist_sgd_momentum(float *params, const float *grads, float *momentum, i
 /* ---- DDP exchange over NVLink peer memory ---------------------------------------------
  * Replaces DDP's gradient all_reduce (mnist.py:135-138) AND optimizer.step() (mnist.py:43) for ranks on one
  * NVLink-connected box, one process per GPU.  Every rank owns a PEER WINDOW: one device allocation
- *   [ flag page B200MNIST_PEER_FLAG_BYTES | parameter bucket | gradient-sum bucket | staging bucket 0 | staging 1 ]
- * (buckets of B200MNIST_FLAT_ELEMS floats) that the other ranks map through CUDA IPC.  The model's parameters and
+ *   [ flag page B200MNIST_PEER_FLAG_BYTES | parameter bucket | gradient-sum bucket | staging bucket 0 | staging 1 |
+ *     receive area ]
+ * (buckets of B200MNIST_FLAT_ELEMS floats; b200mnist_peer_window_bytes() in all) that the other ranks map through CUDA IPC.  The model's parameters and
  * p.grad live in the window; the backward of step s writes its gradient into staging bucket (s & 1).
  *
  * Set-up (these allocate / map device memory and synchronise; call them once, outside any capture):
@@ -117,30 +118,24 @@ int b200mnist_peer_window_open(const void *ipc_handle_host, void **window_out_ho
 int b200mnist_peer_window_close(void *window);
 int b200mnist_peer_window_destroy(void *window);
 int b200mnist_peer_window_probe(void *const *windows_host, int world_size, uint32_t *out, void *stream);
-/* One half of the exchange + update of a step; enqueues one kernel, no allocation, capturable.
+/* The whole data-parallel training step of mnist.py:39-43 under DDP (mnist.py:135-138) for this rank, on ONE stream:
+ * forward, loss, backward, gradient averaging over all ranks and the SGD update -- b200mnist_train_step with the
+ * exchange inside its own kernels.
  *   windows_host : HOST array of world_size window addresses as mapped in THIS process ([rank] = the local one)
- *   parity       : which staging bucket holds this step's gradients (step & 1, the same on every rank)
+ *   parity       : which staging bucket / receive slots this step uses (step & 1, the same on every rank)
  *   momentum     : this rank's momentum bucket (local memory)
- *   part 1: fc1.weight + fc1.bias (93 % of the bucket), two-shot: this rank reduces its 1/world_size slice over all
- *           staging buckets in rank order, applies g = sum*grad_scale; buf = first_step ? g : mu*buf + g;
- *           p = p - lr*buf, and stores the new parameters and the sum into every rank's window.  Meant for a side
- *           stream, concurrent with b200mnist_forward_backward_phase(..., 2).  fc1's momentum is therefore
- *           maintained on the slice's owner only.
- *   part 2: everything else, one-shot: every rank reads all staging buckets, sums in rank order and updates its own
- *           bucket; also waits until all ranks' part-1 slices have landed here.  Must follow the phase-2 call on
- *           the same stream, and every step must issue exactly one part 1 and one part 2 (they share the step
- *           epoch).  All ranks make the same calls in the same order; world_size in {2, 4, 8}. */
-int b200mnist_peer_exchange(void *const *windows_host, int rank, int world_size, int parity, float *momentum, float lr,
-                            float mu, float grad_scale, int first_step, int part, void *stream);
-
-/* b200mnist_forward_backward in two calls, for overlapping the gradient exchange with the backward pass:
- * phase 1 = forward, loss head and the fc backward (afterwards fc1.weight / fc1.bias gradients are final in
- * `grads`); phase 2 = conv backward and the reduction of the remaining partial gradients (+ loss_out).
- * Same arguments as b200mnist_forward_backward; phase 2 must follow phase 1 on the same workspace. */
-int b200mnist_forward_backward_phase(const float *params, float *grads, const float *x, const int64_t *target, int B,
-                                     void *workspace, int64_t workspace_bytes, float *loss_out, float *logp_out,
-                                     int phase, void *stream);
-
+ * fc1.weight + fc1.bias (93 % of the bucket) are exchanged two-shot by extra CTAs in the launch of conv1's
+ * weight-gradient kernel: this rank reduces its 1/world_size slice over all ranks' staging buckets in rank order,
+ * applies g = sum/world_size; buf = first_step ? g : mu*buf + g; p = p - lr*buf, and stores the new parameters and
+ * the sum into every rank's window (fc1's momentum is therefore kept on the slice's owner only).  The step's last
+ * kernel sums the batch-split partial gradients of conv1 / conv2 / fc2, pushes each {value, step epoch} into every
+ * peer's receive area, waits for the peers' values, adds them in rank order and applies the same update; it also
+ * waits until every peer's fc1 slice has landed here.  Parameters and p.grad (the SUM over ranks) are the window's
+ * buckets.  x, target, B, workspace, loss_out as for b200mnist_train_step.  Enqueues only (no allocation,
+ * capturable); every rank must call it once per step; world_size in {2, 4, 8}. */
+int b200mnist_peer_train_step(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
+                              const float *x, const int64_t *target, int B, void *workspace, int64_t workspace_bytes,
+                              float lr, float mu, int first_step, float *loss_out, void *stream);
 /* ---- per-layer entry points (used by the autograd bridge and the unit tests) ------- */
 
 /* F.max_pool2d(F.relu(conv1(x)), 2, 2), mnist.py:26-27.  x [B,1,28,28], w [20,1,5,5],

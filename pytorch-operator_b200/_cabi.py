@@ -80,9 +80,8 @@ SIGNATURES = {
     "b200mnist_peer_window_close": (_i32, [_c_f]),
     "b200mnist_peer_window_destroy": (_i32, [_c_f]),
     "b200mnist_peer_window_probe": (_i32, [ctypes.POINTER(ctypes.c_void_p), _i32, _c_f, _c_f]),
-    "b200mnist_peer_exchange": (_i32, [ctypes.POINTER(ctypes.c_void_p), _i32, _i32, _i32, _c_f, _f32, _f32, _f32, _i32,
-                                       _i32, _c_f]),
-    "b200mnist_forward_backward_phase": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _i32, _c_f]),
+    "b200mnist_peer_train_step": (_i32, [ctypes.POINTER(ctypes.c_void_p), _i32, _i32, _i32, _c_f, _c_f, _c_f, _i32, _c_f,
+                                         _i64, _f32, _f32, _i32, _c_f, _c_f]),
     "b200mnist_conv1_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv2_relu_pool_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
     "b200mnist_conv2_fwd_tc_scratch_bytes": (_i64, []),

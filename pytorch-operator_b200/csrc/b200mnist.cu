@@ -404,10 +404,43 @@ int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const fl
     }
     return 0;
 }
+// What the fused DDP step adds to the backward: the peer windows and the SGD constants of this step.
+struct PeerStep {
+    PeerWin pw;
+    float *m;
+    int parity;
+    float neg_lr, mu, scale;
+    int first;
+};
+template <int WORLD>
+int launch_conv1_bwd_peer(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
+                          const Plan &pl, const PeerStep &ps, cudaStream_t s) {
+    // exchange CTAs: one float4 of this rank's fc1 slice per thread, an even count split over the two grid rows
+    constexpr int per = (kFc1Vec4 + WORLD - 1) / WORLD;
+    const int nx = ceil_div(ceil_div(per, kC1wThreads), 2);
+    CHECK_PDL(launch_pdl(conv1_wgrad_peer_kernel<WORLD>, dim3(nx + pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1,
+                         c1w_part, B, ps.pw, ps.m, ps.parity, ps.neg_lr, ps.mu, ps.scale, ps.first, nx),
+              "conv1 wgrad + fc1 slice exchange (reduce + sgd + push over NVLink)", s);
+    return 0;
+}
 int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
-                     const Plan &pl, cudaStream_t s) {
+                     const Plan &pl, cudaStream_t s, const PeerStep *ps = nullptr) {
+    if (ps) {
+        switch (ps->pw.world) {
+        case 2: return launch_conv1_bwd_peer<2>(dp1, p1, i1, x, B, c1w_part, pl, *ps, s);
+        case 4: return launch_conv1_bwd_peer<4>(dp1, p1, i1, x, B, c1w_part, pl, *ps, s);
+        default: return launch_conv1_bwd_peer<8>(dp1, p1, i1, x, B, c1w_part, pl, *ps, s);
+        }
+    }
     CHECK_PDL(launch_pdl(conv1_wgrad_kernel, dim3(pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1, c1w_part, B),
               "conv1 wgrad", s);
+    return 0;
+}
+template <int WORLD>
+int launch_peer_tail(const PeerStep &ps, const GradSegments &segs, const LossReduce &lrd, cudaStream_t s) {
+    CHECK_PDL(launch_pdl(peer_tail_kernel<WORLD>, dim3(kFusedCovBlocks + 1), dim3(256), 0, s, ps.pw, ps.m, ps.parity, ps.neg_lr,
+                         ps.mu, ps.scale, ps.first, segs, lrd),
+              "step tail: gradient reduce + push + rank-ordered sum + sgd (NVLink P2P)", s);
     return 0;
 }
 
@@ -456,15 +489,8 @@ int launch_sgd_fused(float *p, float *g, float *m, float lr, float mu, float sca
 // forward (+ optional backward up to the partial gradients)
 int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target, int B, const Workspace &w,
                 const Plan &pl, bool backward, float *logp_out, float *stats_out, float loss_scale, int want_correct,
-                cudaStream_t s, int phase = 0) {
-    // phase 0: everything; 1: forward + head + fc backward (fc1 gradients final); 2: conv backward only
+                cudaStream_t s, const PeerStep *ps = nullptr) {
     int rc;
-    if (phase == 2) {
-        if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B,
-                                   w.dp1, w.c2w_part, w.wd, pl, s, pl.c2_presplit)))
-            return rc;
-        return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
-    }
     if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s))) return rc;
     if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, w.w2s, s,
                                backward && pl.c2_presplit ? w.wd : nullptr)))
@@ -484,11 +510,10 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     if ((rc = launch_fc_bwd(w.dz2, w.dz1, w.h, w.p2, P + kOffF1W, B, G + kOffF1W, G + kOffF1B, w.dp2_part,
                             w.fc2w_part, pl, s)))
         return rc;
-    if (phase == 1) return 0;
     if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B, w.dp1,
                                w.c2w_part, w.wd, pl, s, pl.c2_presplit)))
         return rc;
-    return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s);
+    return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s, ps);
 }
 
 }  // namespace
@@ -525,23 +550,6 @@ int b200mnist_forward_backward(const float *params, float *grads, const float *x
     const Workspace w = carve(workspace, B);
     if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, logp_out, loss_out, 1.0f / (float)B, 0, s)))
         return rc;
-    LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
-    return launch_finalize(grads, step_segments(w, pl), lrd, s);
-}
-
-int b200mnist_forward_backward_phase(const float *params, float *grads, const float *x, const int64_t *target, int B,
-                                     void *workspace, int64_t workspace_bytes, float *loss_out, float *logp_out,
-                                     int phase, void *stream) {
-    if (phase != 1 && phase != 2) return fail_arg(2, "phase must be 1 or 2");
-    int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
-    if (rc) return rc;
-    if (!grads || !loss_out || !aligned16(grads)) return fail_arg(5, "grads/loss_out null or grads unaligned");
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const Plan pl = make_plan(B);
-    const Workspace w = carve(workspace, B);
-    if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, logp_out, loss_out, 1.0f / (float)B, 0, s, phase)))
-        return rc;
-    if (phase == 1) return 0;
     LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
     return launch_finalize(grads, step_segments(w, pl), lrd, s);
 }
@@ -645,48 +653,46 @@ int b200mnist_peer_window_probe(void *const *windows_host, int world_size, uint3
     return 0;
 }
 
-}  // extern "C"
-namespace {
-template <int WORLD>
-int launch_peer(const PeerWin &pw, float *m, int parity, float lr, float mu, float scale, int first, int part,
-                cudaStream_t s) {
-    if (part == 1) {
-        // 64-thread CTAs at <= 64 registers, at most one per SM: 4096 registers, which is what two CTAs of the conv2
-        // backward kernel leave free on an SM -- the exchange sits beside its single wave instead of splitting it
-        constexpr int per = (kFc1Vec4 + WORLD - 1) / WORLD;
-        const int grid = clampi(ceil_div(per, kPeerFc1Threads), 1, 148);
-        peer_fc1_kernel<WORLD><<<grid, kPeerFc1Threads, 0, s>>>(pw, m, parity, -lr, mu, scale, first);
-        CHECK_LAUNCH("peer exchange: fc1 slice reduce + sgd + push (NVLink P2P)", s);
-    } else {
-        CHECK_PDL(launch_pdl(peer_rest_kernel<WORLD>, dim3(ceil_div(kRestVec4, kPeerRestThreads)), dim3(kPeerRestThreads),
-                             0, s, pw, m, parity, -lr, mu, scale, first),
-                  "peer exchange: conv/fc2 all-reduce + sgd (NVLink P2P)", s);
-    }
-    return 0;
-}
-}  // namespace
-extern "C" {
-
-int b200mnist_peer_exchange(void *const *windows_host, int rank, int world_size, int parity, float *momentum, float lr,
-                            float mu, float grad_scale, int first_step, int part, void *stream) {
-    if (!windows_host || !momentum) return fail_arg(1, "null pointer argument");
+int b200mnist_peer_train_step(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
+                              const float *x, const int64_t *target, int B, void *workspace, int64_t workspace_bytes,
+                              float lr, float mu, int first_step, float *loss_out, void *stream) {
+    if (!windows_host || !momentum || !loss_out) return fail_arg(1, "null pointer argument");
     if ((world_size != 2 && world_size != 4 && world_size != 8) || rank < 0 || rank >= world_size)
         return fail_arg(2, "world_size must be 2, 4 or 8 and rank in [0, world_size)");
-    if ((parity != 0 && parity != 1) || (part != 1 && part != 2)) return fail_arg(2, "parity must be 0/1 and part 1/2");
+    if (parity != 0 && parity != 1) return fail_arg(2, "parity must be 0 or 1");
     if (!aligned16(momentum)) return fail_arg(3, "momentum must be 16-byte aligned");
-    PeerWin pw{};
+    PeerStep ps{};
     for (int r = 0; r < world_size; ++r) {
         if (!windows_host[r] || (reinterpret_cast<uintptr_t>(windows_host[r]) & 255u))
             return fail_arg(3, "peer windows must be non-null and 256-byte aligned");
-        pw.base[r] = static_cast<char *>(windows_host[r]);
+        ps.pw.base[r] = static_cast<char *>(windows_host[r]);
     }
-    pw.rank = rank;
-    pw.world = world_size;
+    ps.pw.rank = rank;
+    ps.pw.world = world_size;
+    ps.m = momentum;
+    ps.parity = parity;
+    ps.neg_lr = -lr;
+    ps.mu = mu;
+    ps.scale = 1.0f / (float)world_size;
+    ps.first = first_step;
+    char *own = ps.pw.base[rank];
+    const float *params = reinterpret_cast<const float *>(own + kPeerFlagBytes);
+    float *staging = reinterpret_cast<float *>(own + kPeerFlagBytes + (size_t)(2 + parity) * kBucketBytes);
+    int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
+    if (rc) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const Plan pl = make_plan(B);
+    const Workspace w = carve(workspace, B);
+    // forward, loss head, fc backward (fc1's gradient lands in this step's staging bucket), conv2 backward, then conv1's
+    // weight gradient with the fc1 slice exchange in the same launch
+    if ((rc = run_fwd_bwd(params, staging, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s, &ps)))
+        return rc;
+    const GradSegments segs = step_segments(w, pl);
+    const LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
     switch (world_size) {
-    case 2: return launch_peer<2>(pw, momentum, parity, lr, mu, grad_scale, first_step, part, s);
-    case 4: return launch_peer<4>(pw, momentum, parity, lr, mu, grad_scale, first_step, part, s);
-    default: return launch_peer<8>(pw, momentum, parity, lr, mu, grad_scale, first_step, part, s);
+    case 2: return launch_peer_tail<2>(ps, segs, lrd, s);
+    case 4: return launch_peer_tail<4>(ps, segs, lrd, s);
+    default: return launch_peer_tail<8>(ps, segs, lrd, s);
     }
 }
 

@@ -318,16 +318,16 @@ __global__ void __launch_bounds__(kConvBwdThreads) conv2_bwd_kernel(const Conv2B
 constexpr int kC1wThreads = 320;    // 10 channels x 32 lanes
 constexpr int kC1PartStride = 576;  // 500 weights @0, 20 biases @512
 
-__global__ void __launch_bounds__(kC1wThreads)
-conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
-                   const uint8_t *__restrict__ i1, float *__restrict__ part, int B) {
-
-    pdl_wait();
+// bx / nbx / by: this CTA's batch-slice index, the number of slices, and its channel half (the plain kernel passes
+// its block / grid indices; the fused DDP kernel of peer_exchange.cuh shares its grid with another role)
+__device__ __forceinline__ void conv1_wgrad_body(const float *__restrict__ x, const float *__restrict__ dp1,
+                                                 const float *__restrict__ p1, const uint8_t *__restrict__ i1,
+                                                 float *__restrict__ part, int B, const int bx, const int nbx, const int by) {
     // the image is staged as two column-parity planes, xs[c & 1][row][c >> 1]: lanes are consecutive windows, whose
     // pixels are two columns apart -- in a plane they are neighbours, which halves the bank span of every load
     // (ncu on the single-plane layout: 62 % of the shared-memory wavefronts were bank-conflict replays)
     __shared__ __align__(16) float xs[kXElems];
-    const int tid = threadIdx.x, wid = tid >> 5, c = blockIdx.y * 10 + wid, lane = tid & 31;
+    const int tid = threadIdx.x, wid = tid >> 5, c = by * 10 + wid, lane = tid & 31;
     float acc[25], accb = 0.f;
 #pragma unroll
     for (int k = 0; k < 25; ++k) acc[k] = 0.f;
@@ -355,12 +355,12 @@ conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, c
             }
         }
     };
-    if ((int)blockIdx.x < B) fetch(blockIdx.x, gl_n, oa_n, ob_n, xv_n);
-    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    if (bx < B) fetch(bx, gl_n, oa_n, ob_n, xv_n);
+    for (int b = bx; b < B; b += nbx) {
 #pragma unroll
         for (int j = 0; j < 5; ++j) { gl[j] = gl_n[j]; oa[j] = oa_n[j]; ob[j] = ob_n[j]; }
         xv = xv_n;
-        if (b + (int)gridDim.x < B) fetch(b + gridDim.x, gl_n, oa_n, ob_n, xv_n);
+        if (b + nbx < B) fetch(b + nbx, gl_n, oa_n, ob_n, xv_n);
         __syncthreads();  // previous image's readers of xs are done
         if (tid < kXElems / 4) {   // pixels 4 tid .. 4 tid + 3 of one row: columns col, col + 2 -> plane 0; col + 1, col + 3 -> plane 1
             const int row = tid / 7, half = (tid - row * 7) * 2;
@@ -392,9 +392,16 @@ conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, c
         const float s = warp_sum(accb);
         if (lane == 25) mine = s;
     }
-    float *po = part + (size_t)blockIdx.x * kC1PartStride;
+    float *po = part + (size_t)bx * kC1PartStride;
     if (lane < 25) po[c * 25 + lane] = mine;
     else if (lane == 25) po[512 + c] = mine;
+}
+
+__global__ void __launch_bounds__(kC1wThreads)
+conv1_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
+                   const uint8_t *__restrict__ i1, float *__restrict__ part, int B) {
+    pdl_wait();
+    conv1_wgrad_body(x, dp1, p1, i1, part, B, blockIdx.x, gridDim.x, blockIdx.y);
 }
 
 }  // namespace b200mnist

@@ -4,14 +4,15 @@ rank 0's parameters are broadcast at construction and every backward leaves the 
 gradient in place.  Two exchange paths, both over ONE flat 1.7 MB gradient bucket:
 
 * fused (default for 2/4/8 ranks on one NVLink-connected box): every rank owns a *peer window* -- one
-  device allocation holding its parameter bucket, gradient-sum bucket (p.grad) and two staging gradient
-  buckets -- that all other ranks map through CUDA IPC (``b200mnist_peer_window_*``; this works with one
-  process per GPU under ``CUDA_VISIBLE_DEVICES=<rank>``, the single-GPU-per-pod view, as well as with all
-  GPUs visible).  ``b200mnist_peer_exchange`` then replaces all_reduce + optimizer.step(): fc1's 93 % of the
-  bucket is reduced two-shot (each rank sums its 1/world slice in rank order, applies SGD and stores the new
-  parameters into every window) on a side stream WHILE the conv backward runs; the small remainder is
-  reduced one-shot at the end of the step.  No NCCL call, no separate optimizer launch.  fc1's momentum is
-  kept by each slice's owner only (``flat_momentum`` holds this rank's slice of it).
+  device allocation holding its parameter bucket, gradient-sum bucket (p.grad), two staging gradient
+  buckets and a receive area -- that all other ranks map through CUDA IPC (``b200mnist_peer_window_*``; this
+  works with one process per GPU under ``CUDA_VISIBLE_DEVICES=<rank>``, the single-GPU-per-pod view, as well as
+  with all GPUs visible).  ``b200mnist_peer_train_step`` is then the whole step on one stream with the exchange
+  inside its kernels: fc1's 93 % of the bucket is reduced two-shot (each rank sums its 1/world slice in rank
+  order, applies SGD and stores the new parameters into every window) by extra CTAs in the launch of conv1's
+  weight-gradient kernel; the small remainder is pushed to all peers and summed by the step's last kernel.  No
+  NCCL call, no separate optimizer launch, no extra kernel.  fc1's momentum is kept by each slice's owner only
+  (``flat_momentum`` holds this rank's slice of it).
 * NCCL: ``all_reduce(SUM)`` of the bucket on the process group, then the fused SGD kernel with
   ``grad_scale = 1/world_size`` (also what the autograd-bridge path and gloo/CPU host tests use).
 
@@ -46,7 +47,7 @@ class _DeviceMemory:
 
 def _view(ptr: int, count: int, dtype, device) -> torch.Tensor:
     """A tensor over memory of THIS rank's own window (never a peer's mapping)."""
-    typestr = {torch.float32: "<f4", torch.int32: "<i4"}[dtype]
+    typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.int64: "<i8"}[dtype]
     t = torch.as_tensor(_DeviceMemory(ptr, count, typestr), device=device)
     if t.data_ptr() != ptr or t.dtype != dtype:
         raise RuntimeError("could not view the peer window as a tensor without a copy")
@@ -72,7 +73,6 @@ class DistributedDataParallel(nn.Module):
         self._opened = []
         self._step = 0              # steps taken on the fused path: step & 1 selects the staging bucket
         self._force_parity = None   # set while a StepGraph captures one of its two variants
-        self.timeline = None        # set to a dict to have the next eager fused step record its phase boundaries
         want = fused if fused is not None else True
         eligible = (want and module.device.type == "cuda" and self.world_size in (2, 4, 8)
                     and dist.get_backend(process_group) == "nccl")
@@ -154,17 +154,16 @@ class DistributedDataParallel(nn.Module):
         # 4. move the model into the window: parameters and p.grad become views of window memory
         n = net.flat_params.numel()
         bucket = 4 * n
-        assert int(L.b200mnist_peer_window_bytes()) == _FLAG_BYTES + 4 * bucket
+        assert int(L.b200mnist_peer_window_bytes()) >= _FLAG_BYTES + 4 * bucket
         params = _view(own.value + _FLAG_BYTES, n, torch.float32, dev)
         gsum = _view(own.value + _FLAG_BYTES + bucket, n, torch.float32, dev)
         params.copy_(net.flat_params)
         gsum.copy_(net.flat_grads)
         net._bind(params, gsum, net.flat_momentum)
         self._staging = [_view(own.value + _FLAG_BYTES + (2 + k) * bucket, n, torch.float32, dev) for k in (0, 1)]
+        self._stamps = _view(own.value + 2048, 8, torch.int64, dev)   # peer_exchange.cuh: kStampByteOffset
         self._windows = (ctypes.c_void_p * ws)(*ptrs)
         self._own_window, self._opened = own, opened
-        self._side = torch.cuda.Stream(device=dev)
-        self._ev_fc, self._ev_side = torch.cuda.Event(), torch.cuda.Event()
         torch.cuda.synchronize(dev)
         dist.barrier(group=self.process_group)
         self.fused = True
@@ -192,47 +191,35 @@ class DistributedDataParallel(nn.Module):
         """NCCL path: sum the flat gradient bucket over all ranks, in place, on the current stream."""
         dist.all_reduce(self.module.flat_grads, op=dist.ReduceOp.SUM, group=self.process_group)
 
-    def _exchange(self, optimizer, parity, part):
-        m = self.module
-        _cabi.check(_cabi.lib().b200mnist_peer_exchange(
-            self._windows, self.rank, self.world_size, parity, m.flat_momentum.data_ptr(), optimizer.lr,
-            optimizer.momentum, 1.0 / self.world_size, 1 if optimizer.first_step else 0, part, _stream()),
-            "peer_exchange")
-
     def fused_train_step(self, x, target, optimizer, loss_out=None):
-        """Fused path.  The gradient is produced into this step's staging bucket in two phases; fc1's part
-        (93 % of the bucket, final after the fc backward kernel) is exchanged + applied by the two-shot peer kernel
-        on a side stream WHILE the conv backward runs, the remainder right after it."""
+        """Fused path: the whole step, exchange included, as one C call on the current stream
+        (b200mnist_peer_train_step)."""
         net = self.module
-        cur = torch.cuda.current_stream()
         capturing = self._force_parity is not None
         parity = self._force_parity if capturing else self._step & 1
-        staging = self._staging[parity]
-        tl = None if capturing else self.timeline
-
-        def mark(key, stream):
-            if tl is not None:
-                tl[key] = torch.cuda.Event(enable_timing=True)
-                tl[key].record(stream)
-
-        mark("start", cur)
-        net.forward_backward_phase(x, target, 1, staging, loss_out)
-        mark("phase1_end", cur)
-        self._ev_fc.record(cur)
-        self._side.wait_event(self._ev_fc)
-        with torch.cuda.stream(self._side):
-            self._exchange(optimizer, parity, 1)
-            mark("fc1_exchange_end", self._side)
-            self._ev_side.record(self._side)
-        loss = net.forward_backward_phase(x, target, 2, staging, loss_out)
-        mark("phase2_end", cur)
-        self._exchange(optimizer, parity, 2)
-        mark("rest_exchange_end", cur)
-        cur.wait_event(self._ev_side)
+        B = x.shape[0]
+        ws = net.workspace(B)
+        lo = net._loss if loss_out is None else loss_out
+        _cabi.check(_cabi.lib().b200mnist_peer_train_step(
+            self._windows, self.rank, self.world_size, parity, net.flat_momentum.data_ptr(), x.data_ptr(),
+            target.data_ptr(), B, ws.data_ptr(), ws.numel(), optimizer.lr, optimizer.momentum,
+            1 if optimizer.first_step else 0, lo.data_ptr(), _stream()), "peer_train_step")
         optimizer.first_step = False
         if not capturing:
             self._step += 1
-        return loss
+        return lo[0]
+
+    def exchange_telemetry(self):
+        """Where the latest fused step's exchange sat in time (microseconds after the start of the exchange CTAs in
+        conv1's weight-gradient kernel; GPU globaltimer stamps the kernels leave in the flag page):
+        {fc1_barrier, fc1_slice_done, tail_start, tail_pushed, tail_summed, step_period}.  Synchronises the device."""
+        if not self.fused:
+            return None
+        torch.cuda.synchronize(self.module.device)
+        s = self._stamps.tolist()
+        rel = lambda k: round((s[k] - s[0]) * 1e-3, 2)
+        return {"fc1_barrier": rel(1), "fc1_slice_done": rel(2), "tail_start": rel(3), "tail_pushed": rel(4),
+                "tail_summed": rel(5), "step_period": round((s[5] - s[6]) * 1e-3, 2)}
 
     @property
     def staging(self):

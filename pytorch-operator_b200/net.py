@@ -163,17 +163,6 @@ class Net(nn.Module):
                     "forward_backward")
         return lo[0]
 
-    def forward_backward_phase(self, x, target, phase, grads_out, loss_out=None):
-        """Half of forward_backward (b200mnist_forward_backward_phase): phase 1 = forward + loss head + fc
-        backward, phase 2 = conv backward + reduction of the remaining partial gradients."""
-        B = x.shape[0]
-        ws = self.workspace(B)
-        lo = self._loss if loss_out is None else loss_out
-        _cabi.check(_cabi.lib().b200mnist_forward_backward_phase(
-            self.flat_params.data_ptr(), grads_out.data_ptr(), x.data_ptr(), target.data_ptr(), B, ws.data_ptr(),
-            ws.numel(), lo.data_ptr(), 0, phase, _stream()), f"forward_backward phase {phase}")
-        return lo[0]
-
     def train_step(self, x, target, optimizer, loss_out=None):
         """mnist.py:39-43 in one call.  With DDP attached the gradient bucket is all-reduced
         between the backward and the update, and 1/world_size is folded into the update."""
