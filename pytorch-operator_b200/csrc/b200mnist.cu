@@ -357,7 +357,7 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
 }
 int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const float *p2, const uint8_t *i2,
                      const float *p1, const float *w, int B, float *dp1, float *c2w_part, float *wd, const Plan &pl,
-                     cudaStream_t s, bool wd_ready = false) {
+                     cudaStream_t s, bool wd_ready = false, const EarlySignal *sig = nullptr, bool *sig_sent = nullptr) {
     static unsigned long long attr_mask = 0;
     cudaError_t ea = ensure_dynamic_smem(conv2_bwd_kernel, kConv2BwdSmemBytes, &attr_mask);
     if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_bwd)");
@@ -365,7 +365,9 @@ int launch_conv2_bwd(const float *dp2, int nsplit, size_t split_stride, const fl
     a.dp2 = dp2; a.p2 = p2; a.p1 = p1; a.w = w; a.i2 = i2; a.dp1 = dp1; a.part = c2w_part;
     a.split_stride = split_stride; a.nsplit = nsplit; a.B = B;
     a.wg_gy = pl.c2w_split; a.n_wg = 5 * pl.c2w_split; a.dg_gx = pl.c2dg_gx;
+    if (sig) a.sig = *sig;
     const bool dg_tc = pl.c2dg_tc && wd != nullptr;
+    if (sig_sent) *sig_sent = sig && !(dg_tc && pl.c2w_tc);   // the SIMT kernel (which carries the signal) runs at all
     if (!dg_tc && !pl.c2w_tc) {
         CHECK_PDL(launch_pdl(conv2_bwd_kernel, dim3(a.n_wg + 5 * a.dg_gx), dim3(kConvBwdThreads), kConv2BwdSmemBytes, s, a),
                   "conv2 backward (wgrad + dgrad)", s);
@@ -414,22 +416,22 @@ struct PeerStep {
 };
 template <int WORLD>
 int launch_conv1_bwd_peer(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
-                          const Plan &pl, const PeerStep &ps, cudaStream_t s) {
+                          const Plan &pl, const PeerStep &ps, bool presignaled, cudaStream_t s) {
     // exchange CTAs: one float4 of this rank's fc1 slice per thread, an even count split over the two grid rows
     constexpr int per = (kFc1Vec4 + WORLD - 1) / WORLD;
     const int nx = ceil_div(ceil_div(per, kC1wThreads), 2);
     CHECK_PDL(launch_pdl(conv1_wgrad_peer_kernel<WORLD>, dim3(nx + pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1,
-                         c1w_part, B, ps.pw, ps.m, ps.parity, ps.neg_lr, ps.mu, ps.scale, ps.first, nx),
+                         c1w_part, B, ps.pw, ps.m, ps.parity, ps.neg_lr, ps.mu, ps.scale, ps.first, nx, presignaled ? 1 : 0),
               "conv1 wgrad + fc1 slice exchange (reduce + sgd + push over NVLink)", s);
     return 0;
 }
 int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
-                     const Plan &pl, cudaStream_t s, const PeerStep *ps = nullptr) {
+                     const Plan &pl, cudaStream_t s, const PeerStep *ps = nullptr, bool presignaled = false) {
     if (ps) {
         switch (ps->pw.world) {
-        case 2: return launch_conv1_bwd_peer<2>(dp1, p1, i1, x, B, c1w_part, pl, *ps, s);
-        case 4: return launch_conv1_bwd_peer<4>(dp1, p1, i1, x, B, c1w_part, pl, *ps, s);
-        default: return launch_conv1_bwd_peer<8>(dp1, p1, i1, x, B, c1w_part, pl, *ps, s);
+        case 2: return launch_conv1_bwd_peer<2>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
+        case 4: return launch_conv1_bwd_peer<4>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
+        default: return launch_conv1_bwd_peer<8>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
         }
     }
     CHECK_PDL(launch_pdl(conv1_wgrad_kernel, dim3(pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1, c1w_part, B),
@@ -510,10 +512,19 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     if ((rc = launch_fc_bwd(w.dz2, w.dz1, w.h, w.p2, P + kOffF1W, B, G + kOffF1W, G + kOffF1B, w.dp2_part,
                             w.fc2w_part, pl, s)))
         return rc;
+    EarlySignal sig{};
+    bool sig_sent = false;
+    if (ps) {   // the conv2 backward's CTA 0 tells the peers that fc1's gradient is staged (fc backward has completed)
+        for (int r = 0; r < ps->pw.world; ++r)
+            sig.dst[r] = r == ps->pw.rank ? nullptr
+                                          : reinterpret_cast<unsigned *>(ps->pw.base[r]) + kFlagFc1Ready + ps->pw.rank;
+        sig.epoch_src = reinterpret_cast<const unsigned *>(ps->pw.base[ps->pw.rank]) + kFlagEpochA;
+        sig.n = ps->pw.world;
+    }
     if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B, w.dp1,
-                               w.c2w_part, w.wd, pl, s, pl.c2_presplit)))
+                               w.c2w_part, w.wd, pl, s, pl.c2_presplit, ps ? &sig : nullptr, &sig_sent)))
         return rc;
-    return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s, ps);
+    return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s, ps, sig_sent);
 }
 
 }  // namespace

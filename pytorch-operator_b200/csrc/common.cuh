@@ -30,6 +30,28 @@ __device__ __forceinline__ unsigned long long global_ns() {
     return t;
 }
 
+// system-scope release store / acquire load: flags that another GPU polls over NVLink (peer_exchange.cuh)
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// An early "ready" signal a step kernel can carry for the fused DDP exchange: thread t < n of CTA 0 stores
+// *epoch_src + 1 to dst[t] (a flag word in rank t's peer window; nullptr = skip) once the kernel's inputs are complete.
+struct EarlySignal {
+    unsigned *dst[8];
+    const unsigned *epoch_src;
+    int n;
+};
+__device__ __forceinline__ void send_early_signal(const EarlySignal &sig) {
+    const int t = threadIdx.x;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && t < sig.n && sig.dst[t])
+        st_release_sys(sig.dst[t], *reinterpret_cast<const volatile unsigned *>(sig.epoch_src) + 1);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

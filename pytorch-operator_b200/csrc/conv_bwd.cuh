@@ -287,12 +287,14 @@ struct Conv2BwdArgs {
     float *dp1, *part;
     size_t split_stride;
     int nsplit, B, wg_gy, n_wg, dg_gx;
+    EarlySignal sig;   // fused DDP step: tell the peers that this rank's fc1 gradient is staged (n = 0: nothing)
 };
 constexpr int kConv2BwdSmemBytes = kDgSmemFloats * 4;  // 60,000 B dynamic (covers both roles)
 
-__global__ void __launch_bounds__(kConvBwdThreads) conv2_bwd_kernel(const Conv2BwdArgs a) {
+__global__ void __launch_bounds__(kConvBwdThreads) conv2_bwd_kernel(const __grid_constant__ Conv2BwdArgs a) {
 
     pdl_wait();
+    send_early_signal(a.sig);
     extern __shared__ __align__(16) float smem[];
     int b = blockIdx.x;
     if (b < a.n_wg) {

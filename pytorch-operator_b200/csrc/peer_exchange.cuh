@@ -71,14 +71,6 @@ __device__ __forceinline__ unsigned long long *win_recv(char *b, int parity, int
                                                   (size_t)(parity * kMaxPeers + src) * kRecvSlotBytes);
 }
 
-__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
-    unsigned v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
 // one naturally aligned 8-byte access: single-copy atomic, so a reader sees the value and its epoch together
 __device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long *p, unsigned long long v) {
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -137,7 +129,8 @@ constexpr int kFc1Vec4 = (kOffF2W - kOffF1W) / 4;   // fc1.weight + fc1.bias (+ 
 // The fc1 slice exchange as run by exchange CTA `cta` of `ncta`.
 template <int WORLD>
 __device__ __forceinline__ void peer_fc1_slice(const PeerWin &pw, float *__restrict__ m, int parity, float neg_lr,
-                                               float mu, float scale, int first_step, const int cta, const int ncta) {
+                                               float mu, float scale, int first_step, const int cta, const int ncta,
+                                               const int presignaled) {
     const int t = threadIdx.x, rank = pw.rank, nthr = blockDim.x;
     unsigned *flags = win_flags(pw.base[rank]);
     const unsigned epoch = *reinterpret_cast<volatile unsigned *>(flags + kFlagEpochA) + 1;   // written by the tail kernel
@@ -146,8 +139,11 @@ __device__ __forceinline__ void peer_fc1_slice(const PeerWin &pw, float *__restr
         flags[kFlagEpochB] = epoch;   // read by this step's tail kernel, which starts after this kernel has completed
     }
     // ---- "my fc1 gradient is staged" -> every peer; wait for theirs.  (The gradient was written by an earlier
-    //      kernel of this stream, so it is ordered before this release store.)
-    if (cta == 0 && t < WORLD && t != rank) st_release_sys(win_flags(pw.base[t]) + kFlagFc1Ready + rank, epoch);
+    //      kernel of this stream, so it is ordered before this release store.  At small batch the conv2 backward
+    //      kernel has already sent this flag ~20 us ago -- EarlySignal, `presignaled` -- so that nobody waits here
+    //      for a release fence and a flag's flight time.)
+    if (!presignaled && cta == 0 && t < WORLD && t != rank)
+        st_release_sys(win_flags(pw.base[t]) + kFlagFc1Ready + rank, epoch);
     if (t < WORLD && t != rank) spin_until(flags + kFlagFc1Ready + t, epoch);
     __syncthreads();
     if (cta == 0 && t == 0) stamp(flags, 1);
@@ -186,10 +182,11 @@ __global__ void __launch_bounds__(kC1wThreads)
 conv1_wgrad_peer_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
                         const uint8_t *__restrict__ i1, float *__restrict__ part, int B,
                         const __grid_constant__ PeerWin pw, float *__restrict__ m, int parity, float neg_lr, float mu,
-                        float scale, int first_step, int nx) {
+                        float scale, int first_step, int nx, int presignaled) {
     pdl_wait();
     if ((int)blockIdx.x < nx)
-        peer_fc1_slice<WORLD>(pw, m, parity, neg_lr, mu, scale, first_step, blockIdx.y * nx + blockIdx.x, 2 * nx);
+        peer_fc1_slice<WORLD>(pw, m, parity, neg_lr, mu, scale, first_step, blockIdx.y * nx + blockIdx.x, 2 * nx,
+                              presignaled);
     else
         conv1_wgrad_body(x, dp1, p1, i1, part, B, blockIdx.x - nx, gridDim.x - nx, blockIdx.y);
 }
