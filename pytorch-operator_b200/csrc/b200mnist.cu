@@ -325,7 +325,8 @@ int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h,
     return 0;
 }
 int launch_head(const HeadArgs &a, cudaStream_t s) {
-    CHECK_PDL(launch_pdl(head_kernel, dim3(a.B), dim3(kHeadThreads), 0, s, a), "fc2/log_softmax/nll head", s);
+    // one row per CTA up to 4 CTAs on every SM, then several rows per CTA (W2 staged once per CTA)
+    CHECK_PDL(launch_pdl(head_kernel, dim3(a.B < 592 ? a.B : 592), dim3(kHeadThreads), 0, s, a), "fc2/log_softmax/nll head", s);
     return 0;
 }
 int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,

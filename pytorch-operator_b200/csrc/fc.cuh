@@ -288,8 +288,8 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
     __shared__ float red[kHeadThreads];
     __shared__ float red2[kHeadThreads];
     __shared__ bool is_last;
-    const int b = blockIdx.x, t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    // ---- all global loads of the row up front: W2 tile and this thread's two h elements ----
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    // ---- all global loads of the first row up front: W2 tile and this thread's two h elements ----
     float4 wv[5];
 #pragma unroll
     for (int j = 0; j < 5; ++j) {
@@ -297,28 +297,37 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
         wv[j] = i < kClasses * kHElems / 4 ? __ldg(reinterpret_cast<const float4 *>(a.w2) + i)
                                            : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    float hv[2];
+    auto load_row = [&](int b, float (&hv)[2]) {
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const int k = t + j * kHeadThreads;
-        float v = 0.f;
-        if (k < kHElems) {
-            if (a.nsplit > 0) {
-                v = sum_partials<kMaxFc1Split>(a.part + (size_t)b * 512 + k, a.nsplit, (size_t)a.B * 512);
-                v = fmaxf(v + __ldg(a.b1 + k), 0.f);
-                a.h_out[(size_t)b * kHElems + k] = v;
-            } else {
-                v = a.h_in[(size_t)b * kHElems + k];
+        for (int j = 0; j < 2; ++j) {
+            const int k = t + j * kHeadThreads;
+            float v = 0.f;
+            if (k < kHElems) {
+                if (a.nsplit > 0) {
+                    v = sum_partials<kMaxFc1Split>(a.part + (size_t)b * 512 + k, a.nsplit, (size_t)a.B * 512);
+                    v = fmaxf(v + __ldg(a.b1 + k), 0.f);
+                    a.h_out[(size_t)b * kHElems + k] = v;
+                } else {
+                    v = a.h_in[(size_t)b * kHElems + k];
+                }
             }
+            hv[j] = v;
         }
-        hv[j] = v;
-    }
+    };
+    float hv[2], hv_next[2] = {0.f, 0.f};
+    load_row(blockIdx.x, hv_next);
 #pragma unroll
     for (int j = 0; j < 5; ++j) {
         const int i = t + j * kHeadThreads;
         if (i < kClasses * kHElems / 4) reinterpret_cast<float4 *>(w2s)[i] = wv[j];
     }
     __syncthreads();
+    // One row per CTA at the reference batch; at large batch the grid is capped (launch_head) and a CTA walks several
+    // rows with W2 staged once (20 KB per row would otherwise be re-read from L2 4096 times), next row's h in flight.
+    for (int b = blockIdx.x; b < a.B; b += gridDim.x) {
+    hv[0] = hv_next[0];
+    hv[1] = hv_next[1];
+    if (b + (int)gridDim.x < a.B) load_row(b + gridDim.x, hv_next);
     // ---- z = h W2^T + b2 ----
     float acc[kClasses];
 #pragma unroll
@@ -370,16 +379,6 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
             if (!ok) a.rows[b] = __int_as_float(0x7fc00000);  // NaN for an out-of-range target
             if (a.want_correct) a.rows[a.B + b] = (ok && am == (int)tg) ? 1.f : 0.f;
         }
-        if (!a.defer_reduce) {
-            __threadfence();
-            __syncwarp();
-            if (lane == 0) {
-                const unsigned tk = atomicAdd(a.ticket, 1u);
-                is_last = (tk == gridDim.x - 1);
-            }
-        } else if (lane == 0) {
-            is_last = false;
-        }
     }
     __syncthreads();
     if (a.dz1) {
@@ -394,6 +393,15 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
             }
         }
     }
+    }   // rows of this CTA
+    if (t == 0) {
+        is_last = false;
+        if (!a.defer_reduce) {   // this CTA's rows[] entries are written: take a ticket
+            __threadfence();
+            is_last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+        }
+    }
+    __syncthreads();
     if (!is_last) return;
     // ---- deterministic last-CTA reduction of the per-row losses ----
     __threadfence();
