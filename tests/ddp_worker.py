@@ -114,6 +114,41 @@ def property_run(dev, fused, graph=False, steps=6):
     model.close()
 
 
+def soak_run(dev, steps=400):
+    """world_size 2 only: `steps` CUDA-graph replays on the fused path against the same steps on the NCCL path, bit for
+    bit.  With two ranks every summation order gives the same bits (a + b), the SGD kernels round identically, so the
+    two trajectories must stay IDENTICAL -- any race in the fused exchange (a flag seen before its data, a staging
+    bucket or receive slot reused too early, a stale parameter slice) shows up as a differing bit within a few steps."""
+    rank, ws = dist.get_rank(), dist.get_world_size()
+    assert ws == 2
+    batches = [synthetic_batch(64, 9000 + 2 * i + rank) for i in range(8)]
+    batches = [(x.to(dev), t.to(dev)) for x, t in batches]
+    finals = []
+    for fused in (True, False):
+        torch.manual_seed(1)
+        net = pkg.Net().to(dev)
+        model = pkg.DistributedDataParallel(net, fused=fused)
+        assert model.fused == fused, model.fused_error
+        opt = pkg.SGD(model.parameters(), lr=0.01, momentum=0.5)
+        model.train_step(*batches[0], opt)
+        g = pkg.StepGraph(model, opt, 64)
+        losses = []
+        for i in range(1, steps):
+            g.x.copy_(batches[i % 8][0], non_blocking=True)
+            g.target.copy_(batches[i % 8][1], non_blocking=True)
+            g.replay()
+            if i % 50 == 0:
+                losses.append(float(g.loss))
+        torch.cuda.synchronize()
+        finals.append((net.flat_params.clone(), net.flat_grads.clone(), losses))
+        model.release_graphs()
+        model.close()
+    assert finals[0][2] == finals[1][2], ("losses differ", finals[0][2], finals[1][2])
+    assert torch.equal(finals[0][1], finals[1][1]), "last gradient sum differs between the fused and the NCCL path"
+    assert torch.equal(finals[0][0], finals[1][0]), "parameters differ between the fused and the NCCL path"
+    assert finals[0][2][-1] < finals[0][2][0], finals[0][2]
+
+
 def smoke_dist_run(sizes=(4, 431296, 1 << 22), iters=5):
     rank, ws = dist.get_rank(), dist.get_world_size()
     torch.manual_seed(0)
@@ -132,7 +167,9 @@ def main():
     dev = torch.device("cuda", 0 if torch.cuda.device_count() == 1 else rank)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
-    if mode.startswith("prop"):
+    if mode == "soak":
+        soak_run(dev)
+    elif mode.startswith("prop"):
         property_run(dev, fused=mode.startswith("prop-fused"), graph=mode.endswith("graph"))
     else:
         fixture_run(dev, fused=mode.startswith("fused"), graph=mode.endswith("graph"))

@@ -38,6 +38,14 @@ def test_ddp_two_gpus_fused_with_all_gpus_visible():
     assert rc == 0
 
 
+def test_ddp_two_gpus_fused_trajectory_is_bit_identical_to_nccl():
+    """400 CUDA-graph steps on the fused exchange vs the same steps on NCCL all_reduce + SGD: identical bits (a race
+    detector for the flag-free exchange; see ddp_worker.soak_run)."""
+    _need(2)
+    rc = launcher.launch([WORKER, "soak"], workers=1, port=23467, timeout=240)
+    assert rc == 0
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("mode", PROPS)
 def test_ddp_many_gpus_properties(world, mode):
