@@ -51,8 +51,13 @@ def test_device_dataset_matches_torchvision_transform_bit_exact(tmp_path):
     img, lab = sets["train"]
     dl = D.DeviceMNIST.from_files(*D.find_mnist(str(tmp_path), True), batch_size=64, device="cuda:0", shuffle=True, seed=3)
     assert len(dl) == 5 and len(dl.dataset) == 300
-    # ToTensor: uint8 -> float32 / 255 ; Normalize: (x - mean) / std   (torchvision.transforms, mnist.py:121-124)
-    want_all = (torch.from_numpy(img).float().div(255).sub_(D.MNIST_MEAN).div_(D.MNIST_STD)).unsqueeze(1)
+    # the reference's own transform objects (mnist.py:121-124), applied the way datasets.MNIST does: PIL image in
+    from PIL import Image
+    from torchvision import transforms
+    tf = transforms.Compose([transforms.ToTensor(), transforms.Normalize((0.1307,), (0.3081,))])
+    want_all = torch.stack([tf(Image.fromarray(im, mode="L")) for im in img])
+    # and its arithmetic spelled out: uint8 -> float32 / 255, then (x - mean) / std
+    assert torch.equal(want_all, (torch.from_numpy(img).float().div(255).sub_(D.MNIST_MEAN).div_(D.MNIST_STD)).unsqueeze(1))
     seen = []
     for epoch in range(2):
         order = []
