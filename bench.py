@@ -57,6 +57,9 @@ KERNEL_WORK = {
     "fc1 dgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_600_000),
     "fc1 wgrad gemm (tcgen05 3xTF32)": (400_000, 2000 + 3200, 1_602_000),
     "fc1 wgrad + dgrad gemms (tcgen05 3xTF32, one launch)": (800_000, 2000 + 3200 + 3200, 3_202_000),
+    "fc1 operand split (p2 hi/lo)": (0, 3200 + 2 * 3328, 0),
+    "fc1 operand split (W1 hi/lo)": (0, 0, 3 * 1_600_000),
+    "fc1 operand split (dz1 hi/lo)": (0, 3 * 2000, 0),
     "sgd momentum": (0, 0, 5 * PARAM_BYTES),
     "grad finalize": (0, 0, 2 * 31_080 * 4),
 }

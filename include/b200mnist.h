@@ -156,15 +156,18 @@ int64_t b200mnist_conv2_fwd_tc_scratch_bytes(void);
 int b200mnist_conv2_relu_pool_fwd_tc(const float *in, const float *w, const float *bias, float *out, uint8_t *idx,
                                      int B, void *scratch, void *stream);
 /* F.relu(fc1(x)), mnist.py:31.  in [B,800], w [500,800], out [B,500].  `scratch` must hold
- * b200mnist_fc1_scratch_bytes(B) bytes (split-K partial sums). */
+ * b200mnist_fc1_scratch_bytes(B) bytes, 256-byte aligned (split-K partial sums on the fp32 path; hi / lo copies of the
+ * operands on the tensor-core path). */
 int64_t b200mnist_fc1_scratch_bytes(int B);
 int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, float *out, int B, void *scratch,
                            void *stream);
-/* The same F.relu(fc1(x)) (mnist.py:31) forced onto the tensor-core path: TMA-fed tcgen05.mma kind::tf32 with
- * the 3xTF32 error-compensated split (fp32-level accuracy), accumulator in TMEM.  b200mnist_fc1_relu_fwd and the
- * fused step pick it automatically for B >= 384 (B200MNIST_FC1_TC_MIN in the environment moves the threshold);
- * this entry point exists so it can be tested at any B. */
-int b200mnist_fc1_relu_fwd_tc(const float *in, const float *w, const float *bias, float *out, int B, void *stream);
+/* The same F.relu(fc1(x)) (mnist.py:31) forced onto the tensor-core path: both operands are first written to `scratch`
+ * as hi / lo copies (the 3xTF32 error-compensated split, fp32-level accuracy), then a TMA-fed tcgen05.mma kind::tf32
+ * GEMM with its accumulator in TMEM.  b200mnist_fc1_relu_fwd and the fused step pick it automatically for B >= 384
+ * (B200MNIST_FC1_TC_MIN in the environment moves the threshold); this entry point exists so it can be tested at any B.
+ * Same `scratch` as b200mnist_fc1_relu_fwd. */
+int b200mnist_fc1_relu_fwd_tc(const float *in, const float *w, const float *bias, float *out, int B, void *scratch,
+                              void *stream);
 /* F.log_softmax(fc2(h), dim=1) and F.nll_loss (mean), mnist.py:32-33,41, plus the start of
  * loss.backward() (mnist.py:42): dz2 = (softmax - onehot)/B and dz1 = (dz2 . W2) * (h > 0).
  * h [B,500]; logp [B,10]; dz2 [B,10]; dz1 [B,500] (NULL to skip the backward part);
@@ -197,7 +200,7 @@ int b200mnist_fc2_logsoftmax_nll_static(const float *h, const float *w, const fl
 int b200mnist_head_bwd(const float *logp, const float *dlogp, const float *h, const float *w, int B, float *dz2,
                        float *dz1, void *stream);
 /* Backward of the two linear layers, mnist.py:42: gW2 [10,500], gb2 [10], gW1 [500,800],
- * gb1 [500], dp2 [B,800] = dz1 . W1.  scratch: b200mnist_fc_bwd_scratch_bytes(B). */
+ * gb1 [500], dp2 [B,800] = dz1 . W1.  scratch: b200mnist_fc_bwd_scratch_bytes(B), 256-byte aligned. */
 int64_t b200mnist_fc_bwd_scratch_bytes(int B);
 int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
                      float *gw2, float *gb2, float *gw1, float *gb1, float *dp2, void *scratch, void *stream);

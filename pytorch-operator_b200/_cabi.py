@@ -88,7 +88,7 @@ SIGNATURES = {
     "b200mnist_conv2_relu_pool_fwd_tc": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f]),
     "b200mnist_fc1_scratch_bytes": (_i64, [_i32]),
     "b200mnist_fc1_relu_fwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f]),
-    "b200mnist_fc1_relu_fwd_tc": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f]),
+    "b200mnist_fc1_relu_fwd_tc": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f]),
     "b200mnist_fc2_logsoftmax_nll": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f, _c_f, _c_f, _c_f, _c_f]),
     "b200mnist_fc2_logsoftmax_nll_static": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f, _c_f, _c_f, _c_f]),
     "b200mnist_head_bwd": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _c_f, _c_f]),

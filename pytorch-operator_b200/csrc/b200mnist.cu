@@ -160,8 +160,30 @@ struct Workspace {
     float *fc1_part, *dp2_part, *fc2w_part, *c2w_part, *c1w_part;
     float *w2s;  // conv2.weight split into hi/lo tensor-core operands (tc_conv.cuh)
     float *wd;   // the same for the data-gradient GEMM (tc_conv_bwd.cuh)
+    float *fc1ops;  // hi/lo copies of fc1's GEMM operands (Fc1Ops)
     size_t bytes;
 };
+// hi / lo copies of the operands of fc1's three tcgen05 GEMMs (tc_gemm.cuh), written by split_rows_kernel once per step:
+// p2 [B][832] (800 features, column 800 of the hi copy = 1 for the bias gradient, rest zero), dz1 [B][500], W1 [500][800].
+constexpr int kP2Ld = kP2SplitLd;
+constexpr int kFc1TcFloor = 128;   // fc1's tensor-core GEMMs (and their operand copies) exist from this batch up
+struct Fc1Ops {
+    float *p2_hi, *p2_lo, *dz1_hi, *dz1_lo, *w1_hi, *w1_lo;
+};
+inline size_t fc1ops_bytes(int B) {
+    return align256((size_t)B * kP2Ld * 4) * 2 + align256((size_t)B * kHElems * 4) * 2 + align256((size_t)500 * 800 * 4) * 2;
+}
+inline Fc1Ops fc1ops_carve(void *base, int B) {
+    char *p = static_cast<char *>(base);
+    Fc1Ops o;
+    o.p2_hi = reinterpret_cast<float *>(p); p += align256((size_t)B * kP2Ld * 4);
+    o.p2_lo = reinterpret_cast<float *>(p); p += align256((size_t)B * kP2Ld * 4);
+    o.dz1_hi = reinterpret_cast<float *>(p); p += align256((size_t)B * kHElems * 4);
+    o.dz1_lo = reinterpret_cast<float *>(p); p += align256((size_t)B * kHElems * 4);
+    o.w1_hi = reinterpret_cast<float *>(p); p += align256((size_t)500 * 800 * 4);
+    o.w1_lo = reinterpret_cast<float *>(p);
+    return o;
+}
 Workspace carve(void *base, int B) {
     // Partial-sum regions are sized for the worst split of any batch <= B.
     Workspace w;
@@ -191,6 +213,7 @@ Workspace carve(void *base, int B) {
     w.c1w_part = static_cast<float *>(take((size_t)kMaxGradSplit * kC1PartStride * 4));
     w.w2s = static_cast<float *>(take((size_t)tc::kWnScratchFloats * 4));
     w.wd = static_cast<float *>(take((size_t)tc::kDgScratchFloats * 4));
+    w.fc1ops = static_cast<float *>(take(B >= kFc1TcFloor ? fc1ops_bytes(B) : 0));   // never used below that batch
     w.bytes = off;
     return w;
 }
@@ -216,20 +239,26 @@ int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out,
 const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)";
 // conv2 forward on the tensor cores (tcgen05 3xTF32, shifted-window implicit GEMM; tc_conv.cuh).  `w2s` receives the
 // hi/lo-split, operand-ordered copy of conv2.weight (tc::kWnScratchFloats floats), rebuilt on every call.
+// fc1ops (optional): the kernel also writes the hi / lo copies of its output for fc1's tensor-core GEMMs; with wd_also
+// the weight-split launch also writes the hi / lo copies of fc1.weight (w1).
 int launch_conv2_fwd_tc(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B, float *w2s,
-                        cudaStream_t s, float *wd_also = nullptr) {
+                        cudaStream_t s, float *wd_also = nullptr, const Fc1Ops *fc1ops = nullptr, const float *w1 = nullptr) {
     constexpr int NT = 32;
     static unsigned long long attr_mask = 0;
     cudaError_t ea = ensure_dynamic_smem(tc::conv2_fwd_win_kernel<NT>, tc::wn_smem_bytes<NT>(), &attr_mask);
     if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(conv2_fwd_win)");
-    if (wd_also)
-        CHECK_PDL(launch_pdl(tc::conv2_weight_split_both_kernel, dim3(25 + 4 * tc::kDgChunks), dim3(256), 0, s, w, w2s, wd_also),
+    if (wd_also) {
+        const bool with_w1 = fc1ops && w1;
+        CHECK_PDL(launch_pdl(tc::conv2_weight_split_both_kernel, dim3(25 + 4 * tc::kDgChunks + (with_w1 ? ceil_div(500 * 800, 1024) : 0)),
+                             dim3(256), 0, s, w, w2s, wd_also, with_w1 ? w1 : nullptr, with_w1 ? fc1ops->w1_hi : nullptr,
+                             with_w1 ? fc1ops->w1_lo : nullptr),
                   "conv2 weight split (hi/lo; forward + dgrad operands)", s);
-    else
+    } else
         CHECK_PDL(launch_pdl(tc::conv2_weight_split_kernel<NT>, dim3(25), dim3(256), 0, s, w, w2s), "conv2 weight split (hi/lo)", s);
     const int npairs = (B + 1) / 2;
     CHECK_PDL(launch_pdl(tc::conv2_fwd_win_kernel<NT>, dim3(npairs < 74 ? npairs : 74, 64 / NT), dim3(tc::kWnThreads),
-                         (size_t)tc::wn_smem_bytes<NT>(), s, in, (const float *)w2s, b, out, idx, B),
+                         (size_t)tc::wn_smem_bytes<NT>(), s, in, (const float *)w2s, b, out, idx, B,
+                         fc1ops ? fc1ops->p2_hi : nullptr, fc1ops ? fc1ops->p2_lo : nullptr),
               "conv2_relu_pool_fwd (tcgen05 3xTF32 shifted-window GEMM)", s);
     return 0;
 }
@@ -245,7 +274,7 @@ constexpr int kTcConvMinBatch = 128;
 int fc1_tc_min_batch() {   // B200MNIST_FC1_TC_MIN overrides kTcMinBatch (threshold sweeps)
     const char *e = getenv("B200MNIST_FC1_TC_MIN");
     const int v = e ? atoi(e) : 0;
-    return v > 0 ? v : kTcMinBatch;
+    return v > 0 ? (v < kFc1TcFloor ? kFc1TcFloor : v) : kTcMinBatch;
 }
 bool tc_path_enabled(const char *env, int B) {   // read at every (uncaptured) launch: a few hundred ns, lets tests toggle it
     const char *e = getenv(env);
@@ -255,8 +284,8 @@ bool conv2_tc_enabled(int B) { return tc_path_enabled("B200MNIST_CONV2_TC", B); 
 int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
                           cudaStream_t s);
 int launch_conv2_fwd(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B, float *w2s,
-                     cudaStream_t s, float *wd_also = nullptr) {
-    if (w2s && conv2_tc_enabled(B)) return launch_conv2_fwd_tc(in, w, b, out, idx, B, w2s, s, wd_also);
+                     cudaStream_t s, float *wd_also = nullptr, const Fc1Ops *fc1ops = nullptr, const float *w1 = nullptr) {
+    if (w2s && conv2_tc_enabled(B)) return launch_conv2_fwd_tc(in, w, b, out, idx, B, w2s, s, wd_also, fc1ops, w1);
     return launch_conv2_fwd_simt(in, w, b, out, idx, B, s);
 }
 int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float *out, uint8_t *idx, int B,
@@ -266,50 +295,85 @@ int launch_conv2_fwd_simt(const float *in, const float *w, const float *b, float
               "conv2_relu_pool_fwd", s);
     return 0;
 }
-// fc1 forward on the tensor cores (tcgen05 3xTF32, TMA-fed): large batches only (kTcMinBatch).
-template <bool A_MN, bool B_MN, int EPI>
-int launch_tc(const CUtensorMap &ma, const CUtensorMap &mb, const tc::TcGemmArgs &a, const char *what, cudaStream_t s) {
-    static unsigned long long attr_mask = 0;  // one per template instantiation
-    cudaError_t ea = ensure_dynamic_smem(tc::gemm_tc_kernel<A_MN, B_MN, EPI>, tc::kSmemBytes, &attr_mask);
-    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(gemm_tc)");
-    const int ncols = a.N + (EPI == tc::kEpiWgrad ? 1 : 0);  // wgrad carries one extra column (the bias gradient)
-    tc::gemm_tc_kernel<A_MN, B_MN, EPI><<<dim3(ceil_div(ncols, tc::kBN), ceil_div(a.M, tc::kBM)), tc::kThreads,
-                                         tc::kSmemBytes, s>>>(ma, mb, a);
-    CHECK_LAUNCH(what, s);
+// ---- fc1 on the tensor cores (tcgen05 3xTF32, TMA-fed, operands pre-split into hi / lo copies): large batches ----
+int launch_split(const float *in, int ld_in, float *hi, float *lo, int ld_out, int rows, int cols, int ones_col,
+                 const char *what, cudaStream_t s) {
+    const long long n4 = (long long)rows * (ld_out / 4);
+    CHECK_PDL(launch_pdl(tc::split_rows_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, s, in, ld_in, hi, lo, ld_out,
+                         rows, cols, ones_col),
+              what, s);
     return 0;
 }
-
-int launch_fc1_fwd_tc(const float *in, const float *w, const float *bias, float *h, int B, cudaStream_t s) {
-    CUtensorMap ma, mb;
-    if (!tc::make_map_kmajor(&ma, in, B, 800, 800, tc::kBM) || !tc::make_map_kmajor(&mb, w, 500, 800, 800, tc::kBN))
+// maps of a K-major pair (rows x cols, box_rows rows per tile) / an MN-major pair
+bool maps_kmajor(CUtensorMap *hi, CUtensorMap *lo, const float *h, const float *l, int rows, int cols, int ld, int box_rows) {
+    return tc::make_map_kmajor(hi, h, rows, cols, ld, box_rows) && tc::make_map_kmajor(lo, l, rows, cols, ld, box_rows);
+}
+bool maps_mnmajor(CUtensorMap *hi, CUtensorMap *lo, const float *h, const float *l, int rows, int cols, int ld) {
+    return tc::make_map_mnmajor(hi, h, rows, cols, ld) && tc::make_map_mnmajor(lo, l, rows, cols, ld);
+}
+// h = relu(p2 . W1^T + b1): splits p2 (with the bias-gradient column for the backward) and W1, then the GEMM
+// p2_ready / w1_ready: the producer of that operand has already written its hi / lo copies into `o` (the fused step:
+// conv2's tensor-core forward writes p2's, the conv2 weight-split launch W1's); otherwise a split pass runs here.
+int launch_fc1_fwd_tc(const float *in, const float *w, const float *bias, float *h, int B, const Fc1Ops &o, cudaStream_t s,
+                      bool p2_ready = false, bool w1_ready = false) {
+    int rc;
+    if (!p2_ready && (rc = launch_split(in, 800, o.p2_hi, o.p2_lo, kP2Ld, B, 800, 800, "fc1 operand split (p2 hi/lo)", s)))
+        return rc;
+    if (!w1_ready && (rc = launch_split(w, 800, o.w1_hi, o.w1_lo, 800, 500, 800, -1, "fc1 operand split (W1 hi/lo)", s)))
+        return rc;
+    tc::TcMaps m;
+    if (!maps_kmajor(&m.a_hi, &m.a_lo, o.p2_hi, o.p2_lo, B, 800, kP2Ld, tc::kBM) ||
+        !maps_kmajor(&m.b_hi, &m.b_lo, o.w1_hi, o.w1_lo, 500, 800, 800, tc::kBN))
         return fail_arg(8, kTmapErr);
-    tc::TcGemmArgs a{bias, h, nullptr, B, 500, 800, 500};
-    return launch_tc<false, false, tc::kEpiBiasRelu>(ma, mb, a, "fc1 forward gemm (tcgen05 3xTF32)", s);
+    static unsigned long long attr_mask = 0;
+    cudaError_t ea = ensure_dynamic_smem(tc::gemm_tc_kernel<false, false, tc::kEpiBiasRelu>, tc::kSmemBytes, &attr_mask);
+    if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(gemm_tc)");
+    const tc::TcGemmArgs a{bias, h, nullptr, B, 500, 800, 500};
+    CHECK_PDL(launch_pdl(tc::gemm_tc_kernel<false, false, tc::kEpiBiasRelu>, dim3(ceil_div(500, tc::kBN), ceil_div(B, tc::kBM)),
+                         dim3(tc::kThreads), (size_t)tc::kSmemBytes, s, m, a),
+              "fc1 forward gemm (tcgen05 3xTF32)", s);
+    return 0;
 }
 // dp2[B,800] = dz1[B,500] . W1[500,800];  gW1[500,800] = dz1[B,500]^T . p2[B,800], gb1[500] = column sums of dz1:
-// both backward GEMMs of fc1 in one launch (tc::fc1_bwd_tc_kernel)
+// both backward GEMMs of fc1 in one launch (tc::fc1_bwd_tc_kernel).  fwd_ops_ready: the hi / lo copies of p2 and W1
+// are the ones the forward of this step left in `o`; otherwise they are made here.
 int launch_fc1_bwd_tc(const float *dz1, const float *p2, const float *w1, float *gw1, float *gb1, float *dp2, int B,
-                      cudaStream_t s) {
-    CUtensorMap wa, wb, da, db;
-    if (!tc::make_map_mnmajor(&wa, dz1, B, 500, 500) || !tc::make_map_mnmajor(&wb, p2, B, 800, 800) ||
-        !tc::make_map_kmajor(&da, dz1, B, 500, 500, tc::kBM) || !tc::make_map_mnmajor(&db, w1, 500, 800, 800))
+                      const Fc1Ops &o, bool fwd_ops_ready, bool dz1_ready, bool grads_zeroed, cudaStream_t s) {
+    int rc;
+    if (!grads_zeroed) {   // the weight-gradient GEMM adds its two k-halves onto gW1 / gb1 (contiguous in the bucket or not)
+        cudaError_t e = cudaMemsetAsync(gw1, 0, (size_t)500 * 800 * 4, s);
+        if (e == cudaSuccess) e = cudaMemsetAsync(gb1, 0, (size_t)500 * 4, s);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(fc1 gradients)");
+    }
+    if (!fwd_ops_ready) {
+        if ((rc = launch_split(p2, 800, o.p2_hi, o.p2_lo, kP2Ld, B, 800, 800, "fc1 operand split (p2 hi/lo)", s))) return rc;
+        if ((rc = launch_split(w1, 800, o.w1_hi, o.w1_lo, 800, 500, 800, -1, "fc1 operand split (W1 hi/lo)", s))) return rc;
+    }
+    if (!dz1_ready && (rc = launch_split(dz1, 500, o.dz1_hi, o.dz1_lo, 500, B, 500, -1, "fc1 operand split (dz1 hi/lo)", s)))
+        return rc;
+    tc::TcMaps wm, dm;
+    if (!maps_mnmajor(&wm.a_hi, &wm.a_lo, o.dz1_hi, o.dz1_lo, B, 500, 500) ||
+        !maps_mnmajor(&wm.b_hi, &wm.b_lo, o.p2_hi, o.p2_lo, B, 801, kP2Ld) ||   // + the column of ones
+        !maps_kmajor(&dm.a_hi, &dm.a_lo, o.dz1_hi, o.dz1_lo, B, 500, 500, tc::kBM) ||
+        !maps_mnmajor(&dm.b_hi, &dm.b_lo, o.w1_hi, o.w1_lo, 500, 800, 800))
         return fail_arg(8, kTmapErr);
     static unsigned long long attr_mask = 0;
     cudaError_t ea = ensure_dynamic_smem(tc::fc1_bwd_tc_kernel, tc::kSmemBytes, &attr_mask);
     if (ea != cudaSuccess) return fail_cuda(ea, "cudaFuncSetAttribute(fc1_bwd_tc)");
     const tc::TcGemmArgs wg{nullptr, gw1, gb1, 500, 800, B, 800}, dg{nullptr, dp2, nullptr, B, 800, 500, 800};
-    const int wg_gx = ceil_div(800 + 1, tc::kBN), n_wg = wg_gx * ceil_div(500, tc::kBM);   // + the bias-gradient column
+    const int wg_gx = ceil_div(800 + 1, tc::kBN), n_wg = 2 * wg_gx * ceil_div(500, tc::kBM);   // + the bias-gradient column; x 2 k-halves
     const int dg_gx = ceil_div(800, tc::kBN), n_dg = dg_gx * ceil_div(B, tc::kBM);
-    tc::fc1_bwd_tc_kernel<<<dim3(n_wg + n_dg), tc::kThreads, tc::kSmemBytes, s>>>(wa, wb, wg, da, db, dg, wg_gx, n_wg, dg_gx);
-    CHECK_LAUNCH("fc1 wgrad + dgrad gemms (tcgen05 3xTF32, one launch)", s);
+    CHECK_PDL(launch_pdl(tc::fc1_bwd_tc_kernel, dim3(n_wg + n_dg), dim3(tc::kThreads), (size_t)tc::kSmemBytes, s, wm, wg, dm, dg,
+                         wg_gx, n_wg, dg_gx),
+              "fc1 wgrad + dgrad gemms (tcgen05 3xTF32, one launch)", s);
     return 0;
 }
 // fc1 forward: returns the number of split-K partials left in `part` (0 = `h` is final).
 int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h, float *part, int B, const Plan &pl,
-                   cudaStream_t s, int *nsplit_out) {
+                   const Fc1Ops &ops, cudaStream_t s, int *nsplit_out, bool p2_ready = false, bool w1_ready = false) {
     if (B >= fc1_tc_min_batch()) {
         *nsplit_out = 0;
-        return launch_fc1_fwd_tc(in, w, bias, h, B, s);
+        return launch_fc1_fwd_tc(in, w, bias, h, B, ops, s, p2_ready, w1_ready);
     }
     GemmArgs g{};
     g.A = in; g.B = w; g.M = B; g.N = 500; g.K = 800; g.lda = 800; g.ldb = 800; g.kchunk = pl.fc1_kchunk;
@@ -324,13 +388,18 @@ int launch_fc1_fwd(const float *in, const float *w, const float *bias, float *h,
     *nsplit_out = pl.fc1_split == 1 ? 0 : pl.fc1_split;
     return 0;
 }
-int launch_head(const HeadArgs &a, cudaStream_t s) {
+int launch_head(const HeadArgs &a, cudaStream_t s, const HeadTcExtra *x = nullptr) {
     // one row per CTA up to 4 CTAs on every SM, then several rows per CTA (W2 staged once per CTA)
-    CHECK_PDL(launch_pdl(head_kernel, dim3(a.B < 592 ? a.B : 592), dim3(kHeadThreads), 0, s, a), "fc2/log_softmax/nll head", s);
+    const dim3 grid(a.B < 592 ? a.B : 592);
+    if (x)
+        CHECK_PDL(launch_pdl(head_tc_kernel, grid, dim3(kHeadThreads), 0, s, a, *x), "fc2/log_softmax/nll head", s);
+    else
+        CHECK_PDL(launch_pdl(head_kernel, grid, dim3(kHeadThreads), 0, s, a), "fc2/log_softmax/nll head", s);
     return 0;
 }
 int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
-                  float *gw1, float *gb1, float *dp2_part, float *fc2w_part, const Plan &pl, cudaStream_t s) {
+                  float *gw1, float *gb1, float *dp2_part, float *fc2w_part, const Plan &pl, const Fc1Ops &ops,
+                  bool fwd_ops_ready, bool dz1_ready, bool grads_zeroed, cudaStream_t s) {
     const bool use_tc = B >= fc1_tc_min_batch() && pl.dg_split == 1;  // large batch: both fc1 GEMMs on the tensor cores
     FcBwdArgs a{};
     GemmArgs &g = a.wg;  // gW1[n,k] = sum_b dz1[b,n] p2[b,k] ; gb1[n] = sum_b dz1[b,n]
@@ -349,7 +418,7 @@ int launch_fc_bwd(const float *dz2, const float *dz1, const float *h, const floa
     if (use_tc) {
         a.wg_n = 0;
         a.dg_n = 0;  // the SIMT launch keeps only the (tiny) fc2 weight-gradient role
-        int rc = launch_fc1_bwd_tc(dz1, p2, w1, gw1, gb1, dp2_part, B, s);
+        int rc = launch_fc1_bwd_tc(dz1, p2, w1, gw1, gb1, dp2_part, B, ops, fwd_ops_ready, dz1_ready, grads_zeroed, s);
         if (rc) return rc;
     }
     CHECK_PDL(launch_pdl(fc_bwd_kernel, dim3(a.wg_n + a.dg_n + a.fc2_gx * pl.fc2w_split), dim3(256), 0, s, a),
@@ -495,23 +564,32 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
                 cudaStream_t s, const PeerStep *ps = nullptr) {
     int rc;
     if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s))) return rc;
+    // fc1 on the tensor cores reads hi / lo copies of its operands: their producers write them on the way
+    const Fc1Ops ops = fc1ops_carve(w.fc1ops, B);
+    const bool fc1_tc = B >= fc1_tc_min_batch(), c2_tc = w.w2s && conv2_tc_enabled(B);
+    const bool p2_ready = fc1_tc && c2_tc, w1_ready = p2_ready && backward && pl.c2_presplit;
+    const bool fc1_bwd_tc = fc1_tc && backward && pl.dg_split == 1;
     if ((rc = launch_conv2_fwd(w.p1, P + kOffC2W, P + kOffC2B, w.p2, w.i2, B, w.w2s, s,
-                               backward && pl.c2_presplit ? w.wd : nullptr)))
+                               backward && pl.c2_presplit ? w.wd : nullptr, p2_ready ? &ops : nullptr, P + kOffF1W)))
         return rc;
     int nsplit = 0;
-    if ((rc = launch_fc1_fwd(w.p2, P + kOffF1W, P + kOffF1B, w.h, w.fc1_part, B, pl, s, &nsplit))) return rc;
+    if ((rc = launch_fc1_fwd(w.p2, P + kOffF1W, P + kOffF1B, w.h, w.fc1_part, B, pl, ops, s, &nsplit, p2_ready, w1_ready)))
+        return rc;
     HeadArgs a{};
     a.h_in = w.h; a.part = w.fc1_part; a.b1 = P + kOffF1B; a.h_out = w.h;
     a.w2 = P + kOffF2W; a.b2 = P + kOffF2B; a.target = target;
     a.logp = logp_out ? logp_out : w.logp;
     a.dz2 = backward ? w.dz2 : nullptr; a.dz1 = backward ? w.dz1 : nullptr;
+    // fc1 backward on the tensor cores: dz1's hi / lo copies, and fc1.weight + fc1.bias gradients (contiguous in the
+    // bucket) start from zero (see fc1_bwd_tc_kernel)
+    const HeadTcExtra hx{ops.dz1_hi, ops.dz1_lo, reinterpret_cast<float4 *>(G + kOffF1W), (kOffF2W - kOffF1W) / 4};
     a.rows = w.rows; a.ticket = w.ticket; a.stats_out = stats_out;
     a.defer_reduce = backward ? 1 : 0;  // training: the step's last kernel reduces the per-row losses
     a.B = B; a.nsplit = nsplit; a.want_correct = want_correct; a.inv_B = 1.0f / (float)B; a.loss_scale = loss_scale;
-    if ((rc = launch_head(a, s))) return rc;
+    if ((rc = launch_head(a, s, fc1_bwd_tc ? &hx : nullptr))) return rc;
     if (!backward) return 0;
     if ((rc = launch_fc_bwd(w.dz2, w.dz1, w.h, w.p2, P + kOffF1W, B, G + kOffF1W, G + kOffF1B, w.dp2_part,
-                            w.fc2w_part, pl, s)))
+                            w.fc2w_part, pl, ops, fc1_tc, fc1_bwd_tc, fc1_bwd_tc, s)))
         return rc;
     EarlySignal sig{};
     bool sig_sent = false;
@@ -734,7 +812,12 @@ int b200mnist_conv2_relu_pool_fwd_tc(const float *in, const float *w, const floa
     return launch_conv2_fwd_tc(in, w, bias, out, idx, B, static_cast<float *>(scratch), static_cast<cudaStream_t>(stream));
 }
 
-int64_t b200mnist_fc1_scratch_bytes(int B) { return B < 1 ? -1 : (int64_t)10 * B * 512 * 4; }
+// split-K partials (SIMT path) or the hi / lo operand copies (tensor-core path): whichever is larger
+int64_t b200mnist_fc1_scratch_bytes(int B) {
+    if (B < 1) return -1;
+    const int64_t part = (int64_t)10 * B * 512 * 4, ops = (int64_t)fc1ops_bytes(B);
+    return part > ops ? part : ops;
+}
 
 int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, float *out, int B, void *scratch,
                            void *stream) {
@@ -746,14 +829,17 @@ int b200mnist_fc1_relu_fwd(const float *in, const float *w, const float *bias, f
     pl.fc1_split = 1;  // standalone call: finish in the GEMM epilogue, `scratch` stays unused
     pl.fc1_kchunk = 800;
     int nsplit = 0;
-    return launch_fc1_fwd(in, w, bias, out, static_cast<float *>(scratch), B, pl, s, &nsplit);
+    if (reinterpret_cast<uintptr_t>(scratch) & 255u) return fail_arg(3, "scratch must be 256-byte aligned");
+    return launch_fc1_fwd(in, w, bias, out, static_cast<float *>(scratch), B, pl, fc1ops_carve(scratch, B), s, &nsplit);
 }
 
-int b200mnist_fc1_relu_fwd_tc(const float *in, const float *w, const float *bias, float *out, int B, void *stream) {
-    if (!in || !w || !bias || !out) return fail_arg(1, "null pointer argument");
+int b200mnist_fc1_relu_fwd_tc(const float *in, const float *w, const float *bias, float *out, int B, void *scratch,
+                              void *stream) {
+    if (!in || !w || !bias || !out || !scratch) return fail_arg(1, "null pointer argument");
     if (B < 1 || B > 65536) return fail_arg(2, "batch size must be in [1, 65536]");
-    if (!aligned16(in) || !aligned16(w)) return fail_arg(3, "in/w must be 16-byte aligned");
-    return launch_fc1_fwd_tc(in, w, bias, out, B, static_cast<cudaStream_t>(stream));
+    if (!aligned16(in) || !aligned16(w) || (reinterpret_cast<uintptr_t>(scratch) & 255u))
+        return fail_arg(3, "in/w must be 16-byte aligned and scratch 256-byte aligned");
+    return launch_fc1_fwd_tc(in, w, bias, out, B, fc1ops_carve(scratch, B), static_cast<cudaStream_t>(stream));
 }
 
 int b200mnist_fc2_logsoftmax_nll(const float *h, const float *w, const float *bias, const int64_t *target, int B,
@@ -838,8 +924,9 @@ int b200mnist_head_bwd(const float *logp, const float *dlogp, const float *h, co
 }
 
 int64_t b200mnist_fc_bwd_scratch_bytes(int B) {
-    if (B < 1) return -1;
-    return (int64_t)align256((size_t)8 * B * kP2Elems * 4) + (int64_t)32 * kFc2PartStride * 4;
+    if (B < 1) return -1;   // [dp2 split-K partials | fc2 weight-gradient partials | hi / lo operand copies]
+    return (int64_t)align256((size_t)8 * B * kP2Elems * 4) + (int64_t)align256((size_t)32 * kFc2PartStride * 4) +
+           (int64_t)fc1ops_bytes(B);
 }
 
 int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const float *p2, const float *w1, int B,
@@ -853,8 +940,11 @@ int b200mnist_fc_bwd(const float *dz2, const float *dz1, const float *h, const f
     Plan pl = make_plan(B);
     pl.dg_split = 1;  // standalone call: dp2 is written whole
     pl.dg_kchunk = 512;
-    float *fc2w_part = reinterpret_cast<float *>(static_cast<char *>(scratch) + align256((size_t)8 * B * kP2Elems * 4));
-    int rc = launch_fc_bwd(dz2, dz1, h, p2, w1, B, gw1, gb1, dp2, fc2w_part, pl, s);
+    if (reinterpret_cast<uintptr_t>(scratch) & 255u) return fail_arg(3, "scratch must be 256-byte aligned");
+    char *sc = static_cast<char *>(scratch) + align256((size_t)8 * B * kP2Elems * 4);
+    float *fc2w_part = reinterpret_cast<float *>(sc);
+    const Fc1Ops ops = fc1ops_carve(sc + align256((size_t)32 * kFc2PartStride * 4), B);
+    int rc = launch_fc_bwd(dz2, dz1, h, p2, w1, B, gw1, gb1, dp2, fc2w_part, pl, ops, false, false, false, s);
     if (rc) return rc;
     if ((rc = reduce_to(gw2, 5000, fc2w_part, pl.fc2w_split, kFc2PartStride, s))) return rc;
     return reduce_to(gb2, 10, fc2w_part + 5056, pl.fc2w_split, kFc2PartStride, s);

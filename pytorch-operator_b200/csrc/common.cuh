@@ -15,6 +15,11 @@ constexpr int kTensorElems[kNumTensors] = {500, 20, 25000, 50, 400000, 500, 5000
 // Per-image activation sizes (floats).
 constexpr int kXElems = 784, kP1Elems = 2880, kP2Elems = 800, kHElems = 500, kClasses = 10;
 
+// fc1's tcgen05 GEMMs read hi / lo copies of their operands (tc_gemm.cuh): the copy of p2 [B,800] has this leading
+// dimension -- column 800 of the hi copy holds 1 (the bias-gradient column of the weight-gradient GEMM), the rest 0.
+constexpr int kP2SplitLd = 832;
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
 // Programmatic dependent launch, device side.  pdl_wait(): block until the preceding grid on the stream has
 // completed and its writes are visible (returns at once for a normal launch).  pdl_trigger(): allow the next
 // grid to be scheduled as soon as every CTA of this grid has got this far.

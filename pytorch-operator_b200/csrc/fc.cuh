@@ -278,7 +278,16 @@ struct HeadArgs {
     float inv_B, loss_scale;
 };
 
-__global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
+// What the head does on top when the step's fc1 backward runs on the tensor cores (tc_gemm.cuh): hi / lo copies of
+// dz1 (the GEMMs' operand) and clearing of the split-K weight-gradient destination (zero_n float4 at zero_buf).
+struct HeadTcExtra {
+    float *dz1_hi, *dz1_lo;
+    float4 *zero_buf;
+    int zero_n;
+};
+
+template <bool TC_BWD>
+__device__ __forceinline__ void head_body(const HeadArgs &a, const HeadTcExtra &x) {
 
     pdl_wait();
     __shared__ __align__(16) float w2s[kClasses * kHElems];  // 20,000 B
@@ -289,6 +298,9 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
     __shared__ float red2[kHeadThreads];
     __shared__ bool is_last;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    if (TC_BWD && x.zero_buf)
+        for (int i = blockIdx.x * kHeadThreads + t; i < x.zero_n; i += gridDim.x * kHeadThreads)
+            x.zero_buf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     // ---- all global loads of the first row up front: W2 tile and this thread's two h elements ----
     float4 wv[5];
 #pragma unroll
@@ -389,7 +401,13 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
                 float s = 0.f;
 #pragma unroll
                 for (int c = 0; c < kClasses; ++c) s = fmaf(dzs[c], w2s[c * kHElems + k], s);
-                a.dz1[(size_t)b * kHElems + k] = hv[j] > 0.f ? s : 0.f;
+                const float d = hv[j] > 0.f ? s : 0.f;
+                a.dz1[(size_t)b * kHElems + k] = d;
+                if (TC_BWD && x.dz1_hi) {
+                    const float hi = tf32_hi(d);
+                    x.dz1_hi[(size_t)b * kHElems + k] = hi;
+                    x.dz1_lo[(size_t)b * kHElems + k] = d - hi;
+                }
             }
         }
     }
@@ -423,6 +441,9 @@ __global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) {
         *a.ticket = 0u;
     }
 }
+
+__global__ void __launch_bounds__(kHeadThreads) head_kernel(const HeadArgs a) { head_body<false>(a, HeadTcExtra{}); }
+__global__ void __launch_bounds__(kHeadThreads) head_tc_kernel(const HeadArgs a, const HeadTcExtra x) { head_body<true>(a, x); }
 
 // ---------------------------------------------------------------------------------
 // General backward of log_softmax + fc2 for an arbitrary upstream gradient dlogp (the

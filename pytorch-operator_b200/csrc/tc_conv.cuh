@@ -83,7 +83,10 @@ __global__ void __launch_bounds__(256) conv2_weight_split_kernel(const float *__
 template <int NT>
 __global__ void __launch_bounds__(kWnThreads, 1)
 conv2_fwd_win_kernel(const float *__restrict__ in, const float *__restrict__ w2s, const float *__restrict__ bias,
-                     float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
+                     float *__restrict__ out, uint8_t *__restrict__ idx, int B, float *__restrict__ out_hi,
+                     float *__restrict__ out_lo) {
+    // out_hi / out_lo (optional): hi / lo copies of the pooled output with leading dimension kP2SplitLd, the A operand
+    // of fc1's tensor-core GEMMs -- written here so that no separate split pass has to re-read p2
     static_assert(NT == 32, "epilogue reads two 32-column TMEM slabs per tile");
     constexpr int kWBlock = wn_wblock<NT>();
     extern __shared__ uint8_t smem_raw[];
@@ -252,8 +255,19 @@ conv2_fwd_win_kernel(const float *__restrict__ in, const float *__restrict__ w2s
                     if (v2 > best) { best = v2; bi = 2; }
                     if (v3 > best) { best = v3; bi = 3; }
                     const size_t o = ((size_t)b * 50 + oc) * 16 + win;
-                    out[o] = fmaxf(best, 0.f);
+                    const float pv = fmaxf(best, 0.f);
+                    out[o] = pv;
                     idx[o] = (uint8_t)bi;
+                    if (out_hi) {
+                        const size_t f = (size_t)b * kP2SplitLd + oc * 16 + win;
+                        const float hi = tf32_hi(pv);
+                        out_hi[f] = hi;
+                        out_lo[f] = pv - hi;
+                        if (oc == 0 && win == 0) {   // bias-gradient column (columns 801.. only feed discarded outputs)
+                            out_hi[(size_t)b * kP2SplitLd + 800] = 1.0f;
+                            out_lo[(size_t)b * kP2SplitLd + 800] = 0.0f;
+                        }
+                    }
                 }
             }
         }

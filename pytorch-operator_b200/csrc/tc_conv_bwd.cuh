@@ -88,11 +88,22 @@ __global__ void __launch_bounds__(128) conv2_dgrad_weight_split_kernel(const flo
 }
 // Both operand copies of conv2.weight in one launch (training step: the weights do not change between the forward
 // and the backward pass): CTAs [0, 25) build the forward taps, the other 4 x kDgChunks the data-gradient tiles.
+// Blocks beyond those (present when w1 != nullptr) write the hi / lo copies of fc1.weight for fc1's GEMMs, one float4 per thread.
 __global__ void __launch_bounds__(256) conv2_weight_split_both_kernel(const float *__restrict__ w, float *__restrict__ w2s,
-                                                                      float *__restrict__ wd) {
+                                                                      float *__restrict__ wd, const float *__restrict__ w1,
+                                                                      float *__restrict__ w1_hi, float *__restrict__ w1_lo) {
     pdl_wait();
     if (blockIdx.x < 25) conv2_weight_split_block<32>(w, w2s, blockIdx.x);
-    else conv2_dgrad_weight_split_block(w, wd, blockIdx.x - 25);
+    else if (blockIdx.x < 25 + 4 * kDgChunks) conv2_dgrad_weight_split_block(w, wd, blockIdx.x - 25);
+    else {
+        const int i = ((blockIdx.x - 25 - 4 * kDgChunks) * 256 + threadIdx.x) * 4;
+        if (i < 500 * 800) {
+            const float4 x = __ldg(reinterpret_cast<const float4 *>(w1 + i));
+            const float4 h = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
+            *reinterpret_cast<float4 *>(w1_hi + i) = h;
+            *reinterpret_cast<float4 *>(w1_lo + i) = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+        }
+    }
 }
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {

@@ -7,14 +7,16 @@
 // TMEM, tcgen05.commit signals mbarriers, tcgen05.ld brings the tile back for the epilogue.
 //
 // Precision: a single TF32 pass (10-bit mantissa) misses the 1e-5 parity bound by two orders of
-// magnitude, so the kernel does the error-compensated 3xTF32 product.  A warp-specialised
-// "splitter" group turns every fp32 tile that lands in shared memory into hi = x with the low 13
-// mantissa bits cleared (exactly a TF32 number, whatever rounding the MMA applies to its inputs) and
-// lo = x - hi (exact in fp32), in place / at the same offsets, so the swizzled layout TMA produced
-// is preserved without any address arithmetic.  D += A_lo.B_hi + A_hi.B_lo + A_hi.B_hi per k-slice.
+// magnitude, so the kernel does the error-compensated 3xTF32 product: every fp32 operand x is used as
+// hi = x with the low 13 mantissa bits cleared (exactly a TF32 number, whatever rounding the MMA applies
+// to its inputs) and lo = x - hi (exact in fp32);  D += A_lo.B_hi + A_hi.B_lo + A_hi.B_hi per k-slice.
+// The operands arrive PRE-SPLIT: a small elementwise kernel (split_rows_kernel, one pass per operand per
+// step) writes hi and lo copies to the workspace and TMA loads the four tiles of a stage directly -- the
+// first version split every landed tile inside the k-loop with 8 extra warps, and ncu put their
+// fence.proxy.async + barrier traffic, not the MMAs, on the critical path (2-3x the MMA time).
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
-// warps 2-5 = splitters + epilogue (TMEM lane quarter = warp_id % 4).
+// warps 2-5 = TMEM drain + epilogue (TMEM lane quarter = warp_id % 4).
 // Long reductions (wgrad: K = batch): the tensor core's fp32 accumulation error grows with the number
 // of chained MMAs, so every kDrain k-blocks the TMEM tile is folded into fp32 registers (round-to-nearest
 // adds) by the epilogue warps while the MMA continues into the second TMEM accumulator.
@@ -27,17 +29,18 @@
 namespace b200mnist {
 namespace tc {
 
-constexpr int kBM = 128, kBN = 64, kBK = 32;           // CTA tile; kBK fp32 = one 128-byte swizzle row
-constexpr int kStages = 4;
-constexpr int kThreads = 320;           // warp 0: TMA, warp 1: MMA issuer, warps 2-5: split + drain + epilogue, warps 6-9: split only
-constexpr int kSplitters = 256;
-constexpr int kTileA = kBM * kBK * 4, kTileB = kBN * kBK * 4;            // 16,384 B and 8,192 B
-constexpr int kStageBytes = 2 * kTileA + 2 * kTileB;                      // hi + lo of both = 49,152 B
+// CTA tile; kBK fp32 = one 128-byte swizzle row.  With hi and lo copies of both operands a 128 x 64 tile pulled
+// 48 KB from L2 per k-block for 0.39 us of MMA time -- ~8.8 TB/s over all SMs, i.e. L2-bandwidth bound; 128 x 128
+// needs 64 KB for twice the work.
+constexpr int kBM = 128, kBN = 128, kBK = 32;
+constexpr int kStages = 3;
+constexpr int kThreads = 192;           // warp 0: TMA, warp 1: MMA issuer, warps 2-5: TMEM drain + epilogue
+constexpr int kTileA = kBM * kBK * 4, kTileB = kBN * kBK * 4;            // 16,384 B each
+constexpr int kStageBytes = 2 * kTileA + 2 * kTileB;                      // hi + lo of both = 65,536 B
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-static_assert(3 * kStages * 8 + 4 * 8 + 8 <= 256, "barrier area");
-constexpr int kTmemCols = 256;        // two (64 main + 64 small-term) accumulators (ping-pong)
+static_assert(2 * kStages * 8 + 4 * 8 + 8 <= 256, "barrier area");
+constexpr int kTmemCols = 512;        // two (128 main + 128 small-term) accumulators (ping-pong): all of TMEM
 constexpr int kDrain = 8;            // k-blocks (K = 256) accumulated in TMEM before the tile is folded into fp32 registers
-constexpr int kDrainLag = 2;         // the splitters fold group g while they are already 2 k-blocks into group g+1
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -132,28 +135,35 @@ struct TcGemmArgs {
     int M, N, K, ldc;
 };
 
+// The four tensor maps of one GEMM: hi and lo copies of both operands (same shape and layout).
+struct TcMaps {
+    CUtensorMap a_hi, a_lo, b_hi, b_lo;
+};
+
 // A_MN / B_MN: operand is MN-major in global memory (its M / N index is the contiguous one).
-template <bool A_MN, bool B_MN, int EPI>
-__device__ __forceinline__ void gemm_tc_tile(const CUtensorMap &map_a, const CUtensorMap &map_b, const TcGemmArgs &g,
-                                             const int tile_x, const int tile_y) {
+// kEpiWgrad: column N of the B operand is a column of ones in the hi copy (zeros in the lo copy), written by the
+// split pass, so that column N of the product is colsum(A) -- fc1's bias gradient rides in the GEMM.
+// kb0 / kb1: the range of kBK-wide k-blocks this CTA reduces (split-K).  ATOMIC: the tile is ADDED to C / colsum with
+// red.global.add.f32 instead of stored -- used with exactly TWO k-ranges per output tile onto a zeroed destination, so
+// the result is p0 + p1 whichever CTA arrives first (fp32 addition commutes): still bitwise reproducible.
+template <bool A_MN, bool B_MN, int EPI, bool ATOMIC = false>
+__device__ __forceinline__ void gemm_tc_tile(const TcMaps &maps, const TcGemmArgs &g, const int tile_x, const int tile_y,
+                                             const int kb0, const int kb1) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     // stage s: [A_hi | A_lo | B_hi | B_lo]; barriers after the last stage
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes);
-    uint64_t *raw_full = bars, *split_full = bars + kStages, *empty = bars + 2 * kStages;
-    uint64_t *acc_full = bars + 3 * kStages, *acc_empty = bars + 3 * kStages + 2;   // [2] each
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 3 * kStages + 4);
+    uint64_t *full = bars, *empty = bars + kStages;
+    uint64_t *acc_full = bars + 2 * kStages, *acc_empty = bars + 2 * kStages + 2;   // [2] each
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kStages + 4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = tile_y * kBM, n0 = tile_x * kBN;
-    const int nkb = (g.K + kBK - 1) / kBK;
+    const int nkb = kb1 - kb0;
     const int ngroups = (nkb + kDrain - 1) / kDrain;
-    // wgrad: the CTA whose N tile contains column N (= 800) carries the injected column of ones
-    const bool ones_cta = (EPI == kEpiWgrad) && (g.N >= n0) && (g.N < n0 + kBN);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
-            mbar_init(smem_u32(&raw_full[s]), 1);
-            mbar_init(smem_u32(&split_full[s]), kSplitters);
+            mbar_init(smem_u32(&full[s]), 1);
             mbar_init(smem_u32(&empty[s]), 1);
         }
         for (int b = 0; b < 2; ++b) {
@@ -174,28 +184,32 @@ __device__ __forceinline__ void gemm_tc_tile(const CUtensorMap &map_a, const CUt
     const uint32_t tmem_d = *tmem_slot;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer: four tiles per stage (hi and lo of both operands), one transaction barrier =====
         if (lane == 0) {
             for (int kb = 0; kb < nkb; ++kb) {
                 const int s = kb % kStages, ph = (kb / kStages) & 1;
                 mbar_wait(smem_u32(&empty[s]), ph ^ 1);
                 uint8_t *st = smem + s * kStageBytes;
-                const uint32_t bar = smem_u32(&raw_full[s]);
-                mbar_arrive_expect_tx(bar, kTileA + kTileB);
-                // raw fp32 tiles land in the *_hi buffers
-                if (A_MN) {
+                const uint32_t bar = smem_u32(&full[s]);
+                mbar_arrive_expect_tx(bar, kStageBytes);
 #pragma unroll
-                    for (int c = 0; c < kBM / 32; ++c)  // [32 k-rows x 32 m] boxes, 4 KB each
-                        tma_load_2d(smem_u32(st + c * 4096), &map_a, m0 + 32 * c, kb * kBK, bar);
-                } else {
-                    tma_load_2d(smem_u32(st), &map_a, kb * kBK, m0, bar);
-                }
-                if (B_MN) {
+                for (int half = 0; half < 2; ++half) {
+                    const CUtensorMap *ma = half ? &maps.a_lo : &maps.a_hi, *mb = half ? &maps.b_lo : &maps.b_hi;
+                    uint8_t *da = st + half * kTileA, *db = st + 2 * kTileA + half * kTileB;
+                    if (A_MN) {
 #pragma unroll
-                    for (int c = 0; c < kBN / 32; ++c)
-                        tma_load_2d(smem_u32(st + 2 * kTileA + c * 4096), &map_b, n0 + 32 * c, kb * kBK, bar);
-                } else {
-                    tma_load_2d(smem_u32(st + 2 * kTileA), &map_b, kb * kBK, n0, bar);
+                        for (int c = 0; c < kBM / 32; ++c)  // [32 k-rows x 32 m] boxes, 4 KB each
+                            tma_load_2d(smem_u32(da + c * 4096), ma, m0 + 32 * c, (kb0 + kb) * kBK, bar);
+                    } else {
+                        tma_load_2d(smem_u32(da), ma, (kb0 + kb) * kBK, m0, bar);
+                    }
+                    if (B_MN) {
+#pragma unroll
+                        for (int c = 0; c < kBN / 32; ++c)
+                            tma_load_2d(smem_u32(db + c * 4096), mb, n0 + 32 * c, (kb0 + kb) * kBK, bar);
+                    } else {
+                        tma_load_2d(smem_u32(db), mb, (kb0 + kb) * kBK, n0, bar);
+                    }
                 }
             }
         }
@@ -226,7 +240,7 @@ __device__ __forceinline__ void gemm_tc_tile(const CUtensorMap &map_a, const CUt
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             }
             const uint32_t tmem_acc = tm + buf * 2 * kBN;
-            mbar_wait(smem_u32(&split_full[s]), ph);
+            mbar_wait(smem_u32(&full[s]), ph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t a_hi = base16 + s * (kStageBytes >> 4), a_lo = a_hi + (kTileA >> 4), b_hi = a_hi + (2 * kTileA >> 4);
 #pragma unroll
@@ -239,14 +253,12 @@ __device__ __forceinline__ void gemm_tc_tile(const CUtensorMap &map_a, const CUt
             if (kin == kDrain - 1 || kb == nkb - 1) umma_commit_u(smem_u32(&acc_full[buf]), leader);  // group complete
         }
     } else {
-        // ===== splitters (warps 2-9, 256 threads); warps 2-5 also drain TMEM and run the epilogue =====
-        const int t = threadIdx.x - 64;
-        const bool drainer = warp < 6;
+        // ===== warps 2-5 (128 threads): fold each completed accumulator group into fp32 registers, then the epilogue =====
         const int q = warp & 3;            // a warp may only touch its own TMEM lane quarter
         float acc[kBN];
 #pragma unroll
         for (int j = 0; j < kBN; ++j) acc[j] = 0.f;
-        auto drain = [&](int grp) {        // fold accumulator (grp & 1) into the fp32 registers, then hand it back
+        for (int grp = 0; grp < ngroups; ++grp) {
             const int buf = grp & 1;
             mbar_wait(smem_u32(&acc_full[buf]), (grp >> 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -261,60 +273,21 @@ __device__ __forceinline__ void gemm_tc_tile(const CUtensorMap &map_a, const CUt
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             mbar_arrive(smem_u32(&acc_empty[buf]));
-        };
-        int next_drain = 0;
-        for (int kb = 0; kb < nkb; ++kb) {
-            if (drainer && next_drain < ngroups && kb >= (next_drain + 1) * kDrain + kDrainLag) drain(next_drain++);
-            const int s = kb % kStages, ph = (kb / kStages) & 1;
-            mbar_wait(smem_u32(&raw_full[s]), ph);
-            uint8_t *st = smem + s * kStageBytes;
-            uint4 *ah = reinterpret_cast<uint4 *>(st), *al = reinterpret_cast<uint4 *>(st + kTileA);
-            uint4 *bh = reinterpret_cast<uint4 *>(st + 2 * kTileA), *bl = reinterpret_cast<uint4 *>(st + 2 * kTileA + kTileB);
-            auto split = [](uint4 v, uint4 &hi, uint4 &lo) {
-                hi = make_uint4(v.x & 0xFFFFE000u, v.y & 0xFFFFE000u, v.z & 0xFFFFE000u, v.w & 0xFFFFE000u);
-                lo.x = __float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x));
-                lo.y = __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y));
-                lo.z = __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z));
-                lo.w = __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w));
-            };
-#pragma unroll
-            for (int j = 0; j < kTileA / 16 / kSplitters; ++j) {
-                uint4 hi, lo;
-                split(ah[t + j * kSplitters], hi, lo);
-                ah[t + j * kSplitters] = hi;
-                al[t + j * kSplitters] = lo;
-            }
-#pragma unroll
-            for (int j = 0; j < kTileB / 16 / kSplitters; ++j) {
-                uint4 hi, lo;
-                split(bh[t + j * kSplitters], hi, lo);
-                bh[t + j * kSplitters] = hi;
-                bl[t + j * kSplitters] = lo;
-            }
-            if (ones_cta) asm volatile("bar.sync 1, 256;" ::: "memory");  // the split pass has rewritten every vector of B_hi
-            if (ones_cta && t < kBK) {
-                // column n == N of B (all zeros from the out-of-bounds TMA fill) := 1.0 for this k-block's rows:
-                // MN-major chunk c = (N - n0)/32, k-row t at t*128 B, 32-byte unit ((col/8) ^ (t % 4)), float col%8
-                const int col = g.N - n0, c = col >> 5, cc = col & 31;
-                float *row = reinterpret_cast<float *>(st + 2 * kTileA + c * 4096 + t * 128);
-                row[(((cc >> 3) ^ (t & 3)) << 3) + (cc & 7)] = (kb * kBK + t < g.K) ? 1.0f : 0.0f;
-            }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the MMA (async proxy)
-            mbar_arrive(smem_u32(&split_full[s]));
         }
-        while (drainer && next_drain < ngroups) drain(next_drain++);
         // epilogue: registers -> global
         const int row = m0 + q * 32 + lane;
-        if (drainer && row < g.M) {
+        if (row < g.M) {
 #pragma unroll
             for (int j = 0; j < kBN; ++j) {
                 const int n = n0 + j;
                 float v = acc[j];
                 if (n < g.N) {
                     if (EPI == kEpiBiasRelu) v = fmaxf(v + __ldg(g.bias + n), 0.f);
-                    g.C[(size_t)row * g.ldc + n] = v;
+                    if (ATOMIC) atomicAdd(&g.C[(size_t)row * g.ldc + n], v);
+                    else g.C[(size_t)row * g.ldc + n] = v;
                 } else if (EPI == kEpiWgrad && n == g.N) {
-                    g.colsum[row] = v;
+                    if (ATOMIC) atomicAdd(&g.colsum[row], v);
+                    else g.colsum[row] = v;
                 }
             }
         }
@@ -328,25 +301,54 @@ __device__ __forceinline__ void gemm_tc_tile(const CUtensorMap &map_a, const CUt
 
 template <bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-               const TcGemmArgs g) {
-    gemm_tc_tile<A_MN, B_MN, EPI>(map_a, map_b, g, blockIdx.x, blockIdx.y);
+gemm_tc_kernel(const __grid_constant__ TcMaps maps, const TcGemmArgs g) {
+    pdl_wait();
+    gemm_tc_tile<A_MN, B_MN, EPI>(maps, g, blockIdx.x, blockIdx.y, 0, (g.K + kBK - 1) / kBK);
 }
 
 // fc1's two backward GEMMs in ONE launch (they only share dz1): the first n_wg CTAs are weight-gradient tiles
-// (gW1 = dz1^T . p2, K = B: few, long tiles -- 52 CTAs cannot fill 148 SMs on their own), the rest data-gradient
-// tiles (dp2 = dz1 . W1, K = 500: many short ones) that fill the remaining SMs while the long tiles run.
+// (gW1 = dz1^T . p2, K = B: 52 output tiles whose k-loop is the batch -- each is split into TWO k-halves that add
+// their tiles onto the zeroed gradient, 104 CTAs of half the length), the rest data-gradient tiles (dp2 = dz1 . W1,
+// K = 500: many short ones) that fill the remaining SMs while the long tiles run.
 __global__ void __launch_bounds__(kThreads, 1)
-fc1_bwd_tc_kernel(const __grid_constant__ CUtensorMap wg_a, const __grid_constant__ CUtensorMap wg_b, const TcGemmArgs wg,
-                  const __grid_constant__ CUtensorMap dg_a, const __grid_constant__ CUtensorMap dg_b, const TcGemmArgs dg,
-                  const int wg_gx, const int n_wg, const int dg_gx) {
+fc1_bwd_tc_kernel(const __grid_constant__ TcMaps wg_maps, const TcGemmArgs wg, const __grid_constant__ TcMaps dg_maps,
+                  const TcGemmArgs dg, const int wg_gx, const int n_wg, const int dg_gx) {
+    pdl_wait();
     int b = blockIdx.x;
     if (b < n_wg) {
-        gemm_tc_tile<true, true, kEpiWgrad>(wg_a, wg_b, wg, b % wg_gx, b / wg_gx);
+        const int half = b & 1, tile = b >> 1, nkb = (wg.K + kBK - 1) / kBK, mid = (nkb + 1) / 2;
+        gemm_tc_tile<true, true, kEpiWgrad, true>(wg_maps, wg, tile % wg_gx, tile / wg_gx, half ? mid : 0, half ? nkb : mid);
     } else {
         b -= n_wg;
-        gemm_tc_tile<false, true, kEpiStore>(dg_a, dg_b, dg, b % dg_gx, b / dg_gx);
+        gemm_tc_tile<false, true, kEpiStore>(dg_maps, dg, b % dg_gx, b / dg_gx, 0, (dg.K + kBK - 1) / kBK);
     }
+}
+
+// hi / lo copies of a row-major fp32 matrix [rows][cols] (leading dimension ld_in) into two matrices with leading
+// dimension ld_out >= cols (a multiple of 4): hi = x with the low 13 mantissa bits cleared, lo = x - hi.  Columns
+// [cols, ld_out) are padding: zero, except hi[row][ones_col] = 1 when ones_col >= 0 (the wgrad GEMM's bias column).
+// One float4 per thread; cols % 4 == 0.
+__global__ void __launch_bounds__(256)
+split_rows_kernel(const float *__restrict__ in, int ld_in, float *__restrict__ hi, float *__restrict__ lo, int ld_out,
+                  int rows, int cols, int ones_col) {
+    pdl_wait();
+    const int v4 = ld_out >> 2;
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (long long)rows * v4) return;
+    const int r = (int)(idx / v4), c = (int)(idx - (long long)r * v4) * 4;
+    float4 h = make_float4(0.f, 0.f, 0.f, 0.f), l = h;
+    if (c < cols) {
+        const float4 x = __ldg(reinterpret_cast<const float4 *>(in + (size_t)r * ld_in + c));
+        h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u);
+        h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u);
+        h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u);
+        h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u);
+        l = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+    } else if (ones_col >= c && ones_col < c + 4) {
+        (&h.x)[ones_col - c] = 1.0f;
+    }
+    *reinterpret_cast<float4 *>(hi + (size_t)r * ld_out + c) = h;
+    *reinterpret_cast<float4 *>(lo + (size_t)r * ld_out + c) = l;
 }
 
 // ---- host side: tensor maps through the driver entry point (no link-time dependency on libcuda) ----

@@ -20,14 +20,14 @@ def test_fc1_tensor_core_path_matches_fp64(B):
     b = (torch.rand(500, generator=g) - 0.5) * 0.07
     xd, wd, bd = x.to(DEV), w.to(DEV), b.to(DEV)
     out = torch.full((B, 500), 7.0, device=DEV)
-    _cabi.check(L.b200mnist_fc1_relu_fwd_tc(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), out.data_ptr(), B,
+    sc = torch.zeros(int(L.b200mnist_fc1_scratch_bytes(B)), dtype=torch.uint8, device=DEV)
+    _cabi.check(L.b200mnist_fc1_relu_fwd_tc(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), out.data_ptr(), B, sc.data_ptr(),
                                             torch.cuda.current_stream().cuda_stream), "fc1 tc")
     torch.cuda.synchronize()
     ref = torch.relu(x.double() @ w.double().T + b.double())
     assert_close(out.cpu().numpy(), ref.numpy(), rtol=RTOL, what=f"fc1 tcgen05 B={B}")
     # and against the fp32 SIMT kernel (same tolerance)
     out2 = torch.empty(B, 500, device=DEV)
-    sc = torch.zeros(int(L.b200mnist_fc1_scratch_bytes(B)), dtype=torch.uint8, device=DEV)
     if B < 384:  # b200mnist_fc1_relu_fwd itself switches to the tensor-core path from 384 up (kTcMinBatch)
         _cabi.check(L.b200mnist_fc1_relu_fwd(xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), out2.data_ptr(), B,
                                              sc.data_ptr(), torch.cuda.current_stream().cuda_stream), "fc1 simt")
