@@ -266,7 +266,7 @@ def ddp_cpu_worker(rank, world, port, batch, steps, warmup, budget_s, threads, r
         step(i)
     per = torch.tensor([(time.perf_counter() - t0) / max(warmup, 3)])
     dist.all_reduce(per, op=dist.ReduceOp.MAX)
-    n = int(max(1, min(steps, budget_s / float(per))))  # the same count on every rank
+    n = int(max(min(steps, 200), min(steps, budget_s / float(per))))  # the same count on every rank; at least 200
     dist.barrier()
     t0 = time.perf_counter()
     for i in range(n):
