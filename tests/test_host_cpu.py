@@ -210,3 +210,43 @@ def test_pytorchjob_manifests_follow_the_operator_contract(name, module, args):
            [launcher.cluster_spec(job["metadata"]["name"], 7, "worker", i) for i in range(7)]
     assert [e["RANK"] for e in envs] == [str(r) for r in range(total)] and {e["WORLD_SIZE"] for e in envs} == {"8"}
     assert envs[1]["MASTER_ADDR"] == job["metadata"]["name"] + "-master-0" and envs[0]["MASTER_ADDR"] == "localhost"
+
+
+def test_peer_exchange_entry_points_reject_bad_arguments_without_a_gpu():
+    """The fused DDP step's C entry points validate before they touch CUDA: bad world sizes, ranks, parities, null or
+    misaligned windows come back as argument errors (-10000 - k) with a message, never as a launch."""
+    L = _cabi.lib()
+    assert L.b200mnist_peer_window_bytes() == 4096 + 4 * 4 * L.b200mnist_flat_elems() + 2 * 8 * 246272
+    win = (ctypes.c_void_p * 8)(*([0x10000] * 8))
+    mom, x, t, ws, loss = 0x20000, 0x30000, 0x40000, 0x50000, 0x60000
+
+    def step(world=2, rank=0, parity=0, windows=win, momentum=mom, batch=64, ws_bytes=1 << 40):
+        return L.b200mnist_peer_train_step(windows, rank, world, parity, momentum, x, t, batch, ws, ws_bytes, 0.01, 0.5, 0,
+                                           loss, 0)
+
+    for kw in (dict(world=3), dict(world=1), dict(world=16), dict(rank=2), dict(rank=-1), dict(parity=2)):
+        assert step(**kw) == -10002, kw
+        assert _cabi.last_error()
+    assert step(windows=(ctypes.c_void_p * 8)(0x10000, 0)) == -10003          # a window is missing
+    assert step(windows=(ctypes.c_void_p * 8)(0x10000, 0x10010)) == -10003    # not 256-byte aligned
+    assert step(momentum=0) == -10001
+    assert step(momentum=mom + 4) == -10003
+    assert step(batch=0) == -10002
+    assert step(ws_bytes=1024) == -10004 and "workspace" in _cabi.last_error()
+    assert L.b200mnist_peer_window_probe(win, 9, 0x20000, 0) == -10002
+    assert L.b200mnist_peer_window_open(0, ctypes.byref(ctypes.c_void_p())) == -10001
+    assert L.b200mnist_peer_window_close(0) == 0 and L.b200mnist_peer_window_destroy(0) == 0
+    # the workspace map of the saved activations
+    offs = [L.b200mnist_workspace_offset(64, i) for i in range(6)]
+    assert offs == sorted(offs) and offs[0] >= 512 and all(o % 256 == 0 for o in offs)
+    assert L.b200mnist_workspace_offset(64, 6) == -1 and L.b200mnist_workspace_offset(0, 0) == -1
+    assert L.b200mnist_workspace_bytes(4096) > L.b200mnist_workspace_bytes(64) > offs[-1]
+
+
+def test_ddp_worker_batches_are_the_oracles():
+    """tests/ddp_worker.py (also bench.py's parity prologue) draws its batches without importing the oracle: same bits."""
+    from oracle import mnist_oracle as mo
+    from tests import ddp_worker as dw
+    for seed in (0, 1234, 9001):
+        a, b = dw.synthetic_batch(64, seed), mo.synthetic_batch(64, seed)
+        assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
