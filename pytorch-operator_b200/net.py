@@ -84,6 +84,9 @@ class Net(nn.Module):
 
     def _apply(self, fn, recurse=True):
         # .to(device)/.cuda() must move the buckets and re-create the views, not the views.
+        if self._ddp is not None and getattr(self._ddp, "fused", False):
+            raise RuntimeError("this Net's buckets live in a peer window of the fused DDP exchange: call "
+                               "DistributedDataParallel.close() before moving or casting the model")
         self._bind(fn(self.flat_params), fn(self.flat_grads), fn(self.flat_momentum))
         return self
 
