@@ -305,10 +305,11 @@ def _saved_activations(net, B):
     return [v.cpu().numpy().copy() for v in (p1, i1, p2, i2, h)]
 
 
-@pytest.mark.parametrize("B,seed", [(4096, 777), (4096, 31337), (1000, 5)])
+@pytest.mark.parametrize("B,seed", [(4096, 777), (4096, 31337), (1000, 5), (400, 999), (200, 12345), (128, 3)])
 def test_large_batch_gradients_match_c_oracle_on_arbitrary_batches(B, seed):
     """BASELINE configs[4] (B=4096: conv2 forward / data gradient / weight gradient and all three fc1 GEMMs on the
-    tcgen05 3xTF32 kernels) against the C oracle on ARBITRARY batches -- no search for a convenient seed.
+    tcgen05 3xTF32 kernels) and the smaller batches where the tensor-core kernels switch on (conv2 from 128, fc1 from
+    384) against the C oracle on ARBITRARY batches -- no search for a convenient seed.
     The backward takes discrete decisions (max-pool arg-max, three ReLU masks) that an implementation accurate to
     ~1e-6 can legitimately take differently where the deciding value is within rounding of a tie / of zero.  So the
     oracle's backward is teacher-forced with the CUDA run's arg-max maps and masks -- after checking that every
