@@ -79,6 +79,26 @@ int b200mnist_train_step(float *params, float *grads, float *momentum, const flo
                          void *workspace, int64_t workspace_bytes, float lr, float mu, int first_step,
                          float *loss_out, void *stream);
 
+/* "Resident input": the batches of many steps already sit in device memory (a ring of slots) and the step picks its
+ * own -- for training loops that replay one CUDA graph per step with no copy and no host-side pointer in between
+ * (replaces the DataLoader + `data.to(device)` of mnist.py:37-38 when the data fits in HBM).
+ *   slot s: images at x + s * x_stride floats ([B,1,28,28] fp32, 16-byte aligned), targets at target + s * t_stride
+ *   cursor: one uint32 in DEVICE memory: the slot the next step reads.  conv1's forward kernel reads it, the step's
+ *           last kernel sets it to (cursor + 1) % slots.  The host may rewrite it between steps (stream-ordered).
+ * b200mnist_train_step_ring is b200mnist_train_step reading its batch from the ring: `x` and `target` are now OUTPUT
+ * buffers of the step ([B,1,28,28] fp32 and int64[B]): the first kernel leaves the slot's batch there for the rest
+ * of the step (and for the caller to inspect).  ring_host is read during the call only. */
+typedef struct b200mnist_ring {
+    const float *x;
+    const int64_t *target;
+    int64_t x_stride, t_stride;
+    uint32_t slots;
+    uint32_t *cursor;
+} b200mnist_ring_t;
+int b200mnist_train_step_ring(float *params, float *grads, float *momentum, const b200mnist_ring_t *ring_host, float *x,
+                              int64_t *target, int B, void *workspace, int64_t workspace_bytes, float lr, float mu,
+                              int first_step, float *loss_out, void *stream);
+
 /* Replaces model(data) under torch.no_grad() plus the per-batch reductions of test(),
  * mnist.py:56-61: logp_out [B,10] (may be NULL); stats_out[0] = sum of NLL
  * (F.nll_loss(reduction='sum')), stats_out[1] = number of rows whose argmax equals target. */
@@ -136,6 +156,11 @@ int b200mnist_peer_window_probe(void *const *windows_host, int world_size, uint3
 int b200mnist_peer_train_step(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
                               const float *x, const int64_t *target, int B, void *workspace, int64_t workspace_bytes,
                               float lr, float mu, int first_step, float *loss_out, void *stream);
+/* The same step reading its batch from a resident ring (see b200mnist_train_step_ring; every rank has its own ring). */
+int b200mnist_peer_train_step_ring(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
+                                   const b200mnist_ring_t *ring_host, float *x, int64_t *target, int B, void *workspace,
+                                   int64_t workspace_bytes, float lr, float mu, int first_step, float *loss_out,
+                                   void *stream);
 /* ---- per-layer entry points (used by the autograd bridge and the unit tests) ------- */
 
 /* F.max_pool2d(F.relu(conv1(x)), 2, 2), mnist.py:26-27.  x [B,1,28,28], w [20,1,5,5],

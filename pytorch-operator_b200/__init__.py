@@ -4,7 +4,7 @@ sm_100a CUDA kernels behind the C ABI of include/b200mnist.h); this package is t
 Python host side that mirrors the reference payloads' interface."""
 from . import _cabi
 from .ddp import DistributedDataParallel
-from .net import NAMES, Net, StepGraph, StepPipeline
+from .net import NAMES, InputRing, Net, StepGraph, StepPipeline
 from .optim import SGD
 
-__all__ = ["Net", "SGD", "DistributedDataParallel", "StepGraph", "StepPipeline", "NAMES", "_cabi"]
+__all__ = ["Net", "SGD", "DistributedDataParallel", "StepGraph", "StepPipeline", "InputRing", "NAMES", "_cabi"]

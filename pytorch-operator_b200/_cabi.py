@@ -72,8 +72,11 @@ SIGNATURES = {
     "b200mnist_workspace_offset": (_i64, [_i32, _i32]),
     "b200mnist_forward_backward": (_i32, [_c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _c_f]),
     "b200mnist_train_step": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _f32, _f32, _i32, _c_f, _c_f]),
+    "b200mnist_train_step_ring": (_i32, [_c_f, _c_f, _c_f, _c_f, _c_f, _c_f, _i32, _c_f, _i64, _f32, _f32, _i32, _c_f, _c_f]),
     "b200mnist_forward_eval": (_i32, [_c_f, _c_f, _c_f, _i32, _c_f, _i64, _c_f, _c_f, _c_f]),
     "b200mnist_sgd_momentum": (_i32, [_c_f, _c_f, _c_f, _i64, _f32, _f32, _f32, _i32, _c_f]),
+    "b200mnist_peer_train_step_ring": (_i32, [ctypes.POINTER(ctypes.c_void_p), _i32, _i32, _i32, _c_f, _c_f, _c_f, _c_f,
+                                              _i32, _c_f, _i64, _f32, _f32, _i32, _c_f, _c_f]),
     "b200mnist_peer_window_bytes": (_i64, []),
     "b200mnist_peer_window_create": (_i32, [ctypes.POINTER(ctypes.c_void_p), _c_f]),
     "b200mnist_peer_window_open": (_i32, [_c_f, ctypes.POINTER(ctypes.c_void_p)]),
@@ -108,6 +111,14 @@ SIGNATURES = {
     "b200mnist_profile_begin": (_i32, [_c_f, _i32]),
     "b200mnist_profile_end": (_i32, [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), _i32, _c_f]),
 }
+
+
+
+class Ring(ctypes.Structure):
+    """b200mnist_ring_t (include/b200mnist.h)."""
+    _fields_ = [("x", ctypes.c_void_p), ("target", ctypes.c_void_p), ("x_stride", ctypes.c_int64),
+                ("t_stride", ctypes.c_int64), ("slots", ctypes.c_uint32), ("cursor", ctypes.c_void_p)]
+
 
 _lib = None
 

@@ -229,11 +229,33 @@ int check_step_args(const void *params, const void *x, const void *target, int B
 }
 
 // ---- launches of the individual stages ----
-int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out, uint8_t *idx, int B, cudaStream_t s) {
+int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out, uint8_t *idx, int B, cudaStream_t s,
+                     const RingRef *ring = nullptr) {
     // small batches: one CTA per (image, 4-channel group) fills the GPU; large ones: one CTA per image, all groups
-    CHECK_PDL(launch_pdl(conv1_relu_pool_fwd_kernel, dim3(B, B >= 1024 ? 1 : 20 / kC1ChPerCta), dim3(kC1Threads), 0, s, x, w, b,
-                         out, idx, B),
-              "conv1_relu_pool_fwd", s);
+    const dim3 grid(B, B >= 1024 ? 1 : 20 / kC1ChPerCta);
+    if (ring)   // resident input: reads the ring slot under the cursor and fills x / target for the rest of the step
+        CHECK_PDL(launch_pdl(conv1_relu_pool_fwd_ring_kernel, grid, dim3(kC1Threads), 0, s, *ring, w, b, out, idx, B),
+                  "conv1_relu_pool_fwd", s);
+    else
+        CHECK_PDL(launch_pdl(conv1_relu_pool_fwd_kernel, grid, dim3(kC1Threads), 0, s, x, w, b, out, idx, B),
+                  "conv1_relu_pool_fwd", s);
+    return 0;
+}
+// Validates a caller's ring description (include/b200mnist.h) and turns it into the kernels' RingRef; x / target are the
+// step's ordinary input buffers, which conv1's forward kernel fills from the ring.
+int make_ring(const b200mnist_ring_t *ring, const float *x, const int64_t *target, int B, RingRef *out) {
+    if (!ring->x || !ring->target || !ring->cursor) return fail_arg(1, "null pointer in the ring description");
+    if (ring->slots < 1) return fail_arg(2, "the ring needs at least one slot");
+    if (!aligned16(ring->x) || ((ring->x_stride * 4) & 15) || ring->x_stride < (int64_t)B * kXElems || ring->t_stride < B)
+        return fail_arg(3, "ring slots must be 16-byte aligned and at least one batch apart");
+    out->x = ring->x;
+    out->target = reinterpret_cast<const long long *>(ring->target);
+    out->x_stride = ring->x_stride;
+    out->t_stride = ring->t_stride;
+    out->x_copy = const_cast<float *>(x);
+    out->t_copy = reinterpret_cast<long long *>(const_cast<int64_t *>(target));
+    out->cursor = ring->cursor;
+    out->slots = ring->slots;
     return 0;
 }
 const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)";
@@ -561,9 +583,9 @@ int launch_sgd_fused(float *p, float *g, float *m, float lr, float mu, float sca
 // forward (+ optional backward up to the partial gradients)
 int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target, int B, const Workspace &w,
                 const Plan &pl, bool backward, float *logp_out, float *stats_out, float loss_scale, int want_correct,
-                cudaStream_t s, const PeerStep *ps = nullptr) {
+                cudaStream_t s, const PeerStep *ps = nullptr, const RingRef *ring = nullptr) {
     int rc;
-    if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s))) return rc;
+    if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s, ring))) return rc;
     // fc1 on the tensor cores reads hi / lo copies of its operands: their producers write them on the way
     const Fc1Ops ops = fc1ops_carve(w.fc1ops, B);
     const bool fc1_tc = B >= fc1_tc_min_batch(), c2_tc = w.w2s && conv2_tc_enabled(B);
@@ -644,21 +666,43 @@ int b200mnist_forward_backward(const float *params, float *grads, const float *x
     return launch_finalize(grads, step_segments(w, pl), lrd, s);
 }
 
-int b200mnist_train_step(float *params, float *grads, float *momentum, const float *x, const int64_t *target, int B,
-                         void *workspace, int64_t workspace_bytes, float lr, float mu, int first_step,
-                         float *loss_out, void *stream) {
+}  // extern "C"
+namespace {
+int train_step_impl(float *params, float *grads, float *momentum, const float *x, const int64_t *target, int B,
+                    void *workspace, int64_t workspace_bytes, float lr, float mu, int first_step, float *loss_out,
+                    const b200mnist_ring_t *ring, void *stream) {
     int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
     if (rc) return rc;
     if (!grads || !momentum || !loss_out || !aligned16(grads) || !aligned16(momentum))
         return fail_arg(5, "grads/momentum/loss_out null or unaligned");
+    RingRef rr{};
+    if (ring && (rc = make_ring(ring, x, target, B, &rr))) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const Plan pl = make_plan(B);
     const Workspace w = carve(workspace, B);
-    if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s)))
+    if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s, nullptr,
+                          ring ? &rr : nullptr)))
         return rc;
     const GradSegments segs = step_segments(w, pl);
-    LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
+    LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B, ring ? rr.cursor : nullptr, ring ? rr.slots : 0u};
     return launch_sgd_fused(params, grads, momentum, lr, mu, 1.0f, first_step, segs, lrd, s);
+}
+}  // namespace
+extern "C" {
+
+int b200mnist_train_step(float *params, float *grads, float *momentum, const float *x, const int64_t *target, int B,
+                         void *workspace, int64_t workspace_bytes, float lr, float mu, int first_step,
+                         float *loss_out, void *stream) {
+    return train_step_impl(params, grads, momentum, x, target, B, workspace, workspace_bytes, lr, mu, first_step, loss_out,
+                           nullptr, stream);
+}
+
+int b200mnist_train_step_ring(float *params, float *grads, float *momentum, const b200mnist_ring_t *ring_host, float *x,
+                              int64_t *target, int B, void *workspace, int64_t workspace_bytes, float lr, float mu,
+                              int first_step, float *loss_out, void *stream) {
+    if (!ring_host) return fail_arg(1, "null ring description");
+    return train_step_impl(params, grads, momentum, x, target, B, workspace, workspace_bytes, lr, mu, first_step, loss_out,
+                           ring_host, stream);
 }
 
 int b200mnist_forward_eval(const float *params, const float *x, const int64_t *target, int B, void *workspace,
@@ -743,9 +787,11 @@ int b200mnist_peer_window_probe(void *const *windows_host, int world_size, uint3
     return 0;
 }
 
-int b200mnist_peer_train_step(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
-                              const float *x, const int64_t *target, int B, void *workspace, int64_t workspace_bytes,
-                              float lr, float mu, int first_step, float *loss_out, void *stream) {
+}  // extern "C"
+namespace {
+int peer_train_step_impl(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
+                         const float *x, const int64_t *target, int B, void *workspace, int64_t workspace_bytes,
+                         float lr, float mu, int first_step, float *loss_out, const b200mnist_ring_t *ring, void *stream) {
     if (!windows_host || !momentum || !loss_out) return fail_arg(1, "null pointer argument");
     if ((world_size != 2 && world_size != 4 && world_size != 8) || rank < 0 || rank >= world_size)
         return fail_arg(2, "world_size must be 2, 4 or 8 and rank in [0, world_size)");
@@ -770,20 +816,41 @@ int b200mnist_peer_train_step(void *const *windows_host, int rank, int world_siz
     float *staging = reinterpret_cast<float *>(own + kPeerFlagBytes + (size_t)(2 + parity) * kBucketBytes);
     int rc = check_step_args(params, x, target, B, workspace, workspace_bytes);
     if (rc) return rc;
+    RingRef rr{};
+    if (ring && (rc = make_ring(ring, x, target, B, &rr))) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const Plan pl = make_plan(B);
     const Workspace w = carve(workspace, B);
     // forward, loss head, fc backward (fc1's gradient lands in this step's staging bucket), conv2 backward, then conv1's
     // weight gradient with the fc1 slice exchange in the same launch
-    if ((rc = run_fwd_bwd(params, staging, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s, &ps)))
+    if ((rc = run_fwd_bwd(params, staging, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s, &ps,
+                          ring ? &rr : nullptr)))
         return rc;
     const GradSegments segs = step_segments(w, pl);
-    const LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B};
+    const LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B, ring ? rr.cursor : nullptr, ring ? rr.slots : 0u};
     switch (world_size) {
     case 2: return launch_peer_tail<2>(ps, segs, lrd, s);
     case 4: return launch_peer_tail<4>(ps, segs, lrd, s);
     default: return launch_peer_tail<8>(ps, segs, lrd, s);
     }
+}
+}  // namespace
+extern "C" {
+
+int b200mnist_peer_train_step(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
+                              const float *x, const int64_t *target, int B, void *workspace, int64_t workspace_bytes,
+                              float lr, float mu, int first_step, float *loss_out, void *stream) {
+    return peer_train_step_impl(windows_host, rank, world_size, parity, momentum, x, target, B, workspace, workspace_bytes,
+                                lr, mu, first_step, loss_out, nullptr, stream);
+}
+
+int b200mnist_peer_train_step_ring(void *const *windows_host, int rank, int world_size, int parity, float *momentum,
+                                   const b200mnist_ring_t *ring_host, float *x, int64_t *target, int B, void *workspace,
+                                   int64_t workspace_bytes, float lr, float mu, int first_step, float *loss_out,
+                                   void *stream) {
+    if (!ring_host) return fail_arg(1, "null ring description");
+    return peer_train_step_impl(windows_host, rank, world_size, parity, momentum, x, target, B, workspace, workspace_bytes,
+                                lr, mu, first_step, loss_out, ring_host, stream);
 }
 
 int b200mnist_conv1_relu_pool_fwd(const float *x, const float *w, const float *bias, float *out, uint8_t *idx, int B,

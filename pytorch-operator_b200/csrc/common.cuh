@@ -57,6 +57,20 @@ __device__ __forceinline__ void send_early_signal(const EarlySignal &sig) {
         st_release_sys(sig.dst[t], *reinterpret_cast<const volatile unsigned *>(sig.epoch_src) + 1);
 }
 
+// "Resident input": a ring of batches that already sits in device memory plus a device-side cursor, so that a
+// CUDA-graph replay of the step needs no copy and no host-side pointer: conv1's forward kernel reads slot *cursor
+// (x + slot * x_stride floats, target + slot * t_stride elements), leaves copies in the step's ordinary input buffers
+// (x_copy / t_copy: what the later kernels of the step read) and the step's last kernel advances the cursor.
+struct RingRef {
+    const float *x;
+    const long long *target;
+    long long x_stride, t_stride;
+    float *x_copy;
+    long long *t_copy;
+    unsigned *cursor;
+    unsigned slots;
+};
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -20,11 +20,11 @@ namespace b200mnist {
 constexpr int kC1ChPerCta = 4;
 constexpr int kC1Threads = 160;
 
-__global__ void __launch_bounds__(kC1Threads)
-conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ bias,
-                           float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
-
-    pdl_wait();
+// x_copy (ring variant only): the image is also stored there, for the later kernels of the step
+template <bool COPY>
+__device__ __forceinline__ void conv1_fwd_body(const float *__restrict__ x, const float *__restrict__ w,
+                                               const float *__restrict__ bias, float *__restrict__ out,
+                                               uint8_t *__restrict__ idx, int B, float *__restrict__ x_copy) {
     __shared__ __align__(16) float xs[kXElems];
     __shared__ __align__(16) float ws[5][25 * kC1ChPerCta];
     __shared__ float bs[20];
@@ -32,6 +32,11 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
     const float4 *xg = reinterpret_cast<const float4 *>(x + (size_t)b * kXElems);
     float4 xv0 = __ldg(xg + t), xv1 = make_float4(0.f, 0.f, 0.f, 0.f);
     if (t + kC1Threads < kXElems / 4) xv1 = __ldg(xg + t + kC1Threads);
+    if (COPY && blockIdx.y == 0) {
+        float4 *xc = reinterpret_cast<float4 *>(x_copy + (size_t)b * kXElems);
+        xc[t] = xv0;
+        if (t + kC1Threads < kXElems / 4) xc[t + kC1Threads] = xv1;
+    }
     for (int cg = blockIdx.y; cg < 5; cg += gridDim.y) {   // this CTA's channel groups: [tap][4 channels] each
         if (t < 25 * kC1ChPerCta) ws[cg][(t % 25) * kC1ChPerCta + t / 25] = __ldg(w + cg * kC1ChPerCta * 25 + t);
         if (t < kC1ChPerCta) bs[cg * kC1ChPerCta + t] = __ldg(bias + cg * kC1ChPerCta + t);
@@ -90,6 +95,24 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
         idx[o] = (uint8_t)bi;
     }
     }
+}
+
+__global__ void __launch_bounds__(kC1Threads)
+conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ bias,
+                           float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
+    pdl_wait();
+    conv1_fwd_body<false>(x, w, bias, out, idx, B, nullptr);
+}
+
+// The same from a resident ring (RingRef): the cursor is read after the previous step's last kernel, which advanced
+// it, has completed; CTA (b, 0) also forwards target b.
+__global__ void __launch_bounds__(kC1Threads)
+conv1_relu_pool_fwd_ring_kernel(const RingRef r, const float *__restrict__ w, const float *__restrict__ bias,
+                                float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
+    pdl_wait();
+    const unsigned slot = *reinterpret_cast<const volatile unsigned *>(r.cursor);
+    if (blockIdx.y == 0 && threadIdx.x == 0) r.t_copy[blockIdx.x] = r.target[(long long)slot * r.t_stride + blockIdx.x];
+    conv1_fwd_body<true>(r.x + (long long)slot * r.x_stride, w, bias, out, idx, B, r.x_copy);
 }
 
 // ---------------------------------------------------------------------------------

@@ -52,7 +52,15 @@ struct LossReduce {   // rows == nullptr: nothing to do
     float *out;
     int B;
     float scale;
+    unsigned *cursor;   // resident-input steps (RingRef): the block that reduces the loss also advances the ring cursor
+    unsigned slots;
 };
+__device__ __forceinline__ void advance_cursor(const LossReduce &lr) {
+    if (lr.cursor && threadIdx.x == 0) {
+        const unsigned c = *lr.cursor + 1;
+        *lr.cursor = c >= lr.slots ? 0u : c;
+    }
+}
 
 // Writes the summed partials into the flat gradient bucket (the tensors that come out of
 // batch-split kernels); everything else in the bucket is already final.
@@ -171,8 +179,9 @@ sgd_fused_kernel(float *__restrict__ p, float *__restrict__ g, float *__restrict
         }
         *reinterpret_cast<float4 *>(m + i4) = make_float4(ms[0], ms[1], ms[2], ms[3]);
         *reinterpret_cast<float4 *>(p + i4) = make_float4(ps[0], ps[1], ps[2], ps[3]);
-    } else if (lr.rows) {
-        reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
+    } else {
+        if (lr.rows) reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
+        advance_cursor(lr);
     }
 }
 

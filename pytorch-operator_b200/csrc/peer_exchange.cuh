@@ -217,6 +217,7 @@ peer_tail_kernel(const __grid_constant__ PeerWin pw, float *__restrict__ m, int 
         if (t < WORLD && t != rank) st_release_sys(win_flags(pw.base[t]) + kFlagFc1Pushed + rank, epoch);
         if (t == 0) flags[kFlagEpochA] = epoch;   // read by the next step's exchange CTAs
         if (lr.rows) reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
+        advance_cursor(lr);
         // the step is over when every peer's fc1 slice has landed in this rank's window as well
         if (t < WORLD && t != rank) spin_until(flags + kFlagFc1Pushed + t, epoch);
         return;

@@ -191,19 +191,23 @@ class DistributedDataParallel(nn.Module):
         """NCCL path: sum the flat gradient bucket over all ranks, in place, on the current stream."""
         dist.all_reduce(self.module.flat_grads, op=dist.ReduceOp.SUM, group=self.process_group)
 
-    def fused_train_step(self, x, target, optimizer, loss_out=None):
+    def fused_train_step(self, x, target, optimizer, loss_out=None, ring=None):
         """Fused path: the whole step, exchange included, as one C call on the current stream
-        (b200mnist_peer_train_step)."""
+        (b200mnist_peer_train_step; with ``ring`` the batch comes from this rank's resident InputRing)."""
         net = self.module
         capturing = self._force_parity is not None
         parity = self._force_parity if capturing else self._step & 1
         B = x.shape[0]
         ws = net.workspace(B)
         lo = net._loss if loss_out is None else loss_out
-        _cabi.check(_cabi.lib().b200mnist_peer_train_step(
-            self._windows, self.rank, self.world_size, parity, net.flat_momentum.data_ptr(), x.data_ptr(),
-            target.data_ptr(), B, ws.data_ptr(), ws.numel(), optimizer.lr, optimizer.momentum,
-            1 if optimizer.first_step else 0, lo.data_ptr(), _stream()), "peer_train_step")
+        L = _cabi.lib()
+        head = (self._windows, self.rank, self.world_size, parity, net.flat_momentum.data_ptr())
+        tail = (x.data_ptr(), target.data_ptr(), B, ws.data_ptr(), ws.numel(), optimizer.lr, optimizer.momentum,
+                1 if optimizer.first_step else 0, lo.data_ptr(), _stream())
+        if ring is None:
+            _cabi.check(L.b200mnist_peer_train_step(*head, *tail), "peer_train_step")
+        else:
+            _cabi.check(L.b200mnist_peer_train_step_ring(*head, ring.desc_ptr, *tail), "peer_train_step_ring")
         optimizer.first_step = False
         if not capturing:
             self._step += 1
@@ -229,8 +233,8 @@ class DistributedDataParallel(nn.Module):
     def forward(self, x):
         return self.module(x)
 
-    def train_step(self, x, target, optimizer, loss_out=None):
-        return self.module.train_step(x, target, optimizer, loss_out=loss_out)
+    def train_step(self, x, target, optimizer, loss_out=None, ring=None):
+        return self.module.train_step(x, target, optimizer, loss_out=loss_out, ring=ring)
 
     def evaluate(self, *a, **k):
         return self.module.evaluate(*a, **k)

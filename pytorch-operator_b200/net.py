@@ -38,6 +38,43 @@ def flat_layout():
             for i, (n, s) in enumerate(zip(NAMES, SHAPES))]
 
 
+class InputRing:
+    """Batches that already sit in device memory plus a device-side cursor (``b200mnist_ring_t``): a step called with
+    ``ring=`` reads the slot under the cursor in its first kernel and advances the cursor in its last one, so a loop
+    of CUDA-graph replays needs no per-step copy and no host-side pointer (what the reference does with a DataLoader
+    and ``data.to(device)``, mnist.py:37-38, when the data fits in HBM).
+
+    ``records``: uint8 [slots, B*784*4 + B*8], each row one packed batch (fp32 images, then int64 targets) -- or pass
+    ``x`` [slots,B,1,28,28] float32 and ``target`` [slots,B] int64."""
+
+    def __init__(self, batch, records=None, x=None, target=None):
+        import ctypes
+        self.batch = batch
+        if records is not None:
+            xb = batch * 784 * 4
+            if records.dtype != torch.uint8 or records.dim() != 2 or records.shape[1] != xb + batch * 8 \
+                    or not records.is_contiguous() or records.shape[1] % 16:
+                raise ValueError("records must be contiguous uint8 [slots, B*784*4 + B*8] with 16-byte aligned rows")
+            self._keep = (records,)
+            x_ptr, t_ptr = records.data_ptr(), records.data_ptr() + xb
+            x_stride, t_stride, slots, dev = records.shape[1] // 4, records.shape[1] // 8, records.shape[0], records.device
+        else:
+            if x.dtype != torch.float32 or target.dtype != torch.int64 or not x.is_contiguous() \
+                    or not target.is_contiguous() or tuple(x.shape[1:]) != (batch, 1, 28, 28) \
+                    or tuple(target.shape) != (x.shape[0], batch):
+                raise ValueError("x must be float32 [slots,B,1,28,28] and target int64 [slots,B], both contiguous")
+            self._keep = (x, target)
+            x_ptr, t_ptr, x_stride, t_stride, slots, dev = x.data_ptr(), target.data_ptr(), batch * 784, batch, x.shape[0], x.device
+        self.slots, self.device = slots, dev
+        self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.desc = _cabi.Ring(x_ptr, t_ptr, x_stride, t_stride, slots, self.cursor.data_ptr())
+        self.desc_ptr = ctypes.addressof(self.desc)
+
+    def seek(self, slot: int):
+        """Point the cursor at ``slot`` (stream-ordered)."""
+        self.cursor.fill_(int(slot) % self.slots)
+
+
 class _Leaf(nn.Module):
     """Holds ``weight`` and ``bias`` so state_dict keys match the reference's layers."""
 
@@ -166,25 +203,34 @@ class Net(nn.Module):
                     "forward_backward")
         return lo[0]
 
-    def train_step(self, x, target, optimizer, loss_out=None):
+    def train_step(self, x, target, optimizer, loss_out=None, ring=None):
         """mnist.py:39-43 in one call.  With DDP attached the gradient bucket is all-reduced
-        between the backward and the update, and 1/world_size is folded into the update."""
+        between the backward and the update, and 1/world_size is folded into the update.
+        ``ring`` (an ``InputRing``): the batch comes from the ring slot under its cursor; ``x`` / ``target`` are then
+        the buffers the step leaves that batch in."""
+        if ring is not None and (ring.batch != x.shape[0] or ring.device != self.device):
+            raise ValueError("the ring holds batches of another size or on another device")
         if self._ddp is None:
             lo = self._loss if loss_out is None else loss_out
             x = self._check_inputs(x, target)
             B = x.shape[0]
             ws = self.workspace(B)
             L = _cabi.lib()
-            _cabi.check(L.b200mnist_train_step(self.flat_params.data_ptr(), self.flat_grads.data_ptr(),
-                                               self.flat_momentum.data_ptr(), x.data_ptr(), target.data_ptr(), B,
-                                               ws.data_ptr(), ws.numel(), optimizer.lr, optimizer.momentum,
-                                               1 if optimizer.first_step else 0, lo.data_ptr(), _stream()),
-                        "train_step")
+            tail = (B, ws.data_ptr(), ws.numel(), optimizer.lr, optimizer.momentum, 1 if optimizer.first_step else 0,
+                    lo.data_ptr(), _stream())
+            head = (self.flat_params.data_ptr(), self.flat_grads.data_ptr(), self.flat_momentum.data_ptr())
+            if ring is None:
+                _cabi.check(L.b200mnist_train_step(*head, x.data_ptr(), target.data_ptr(), *tail), "train_step")
+            else:
+                _cabi.check(L.b200mnist_train_step_ring(*head, ring.desc_ptr, x.data_ptr(), target.data_ptr(), *tail),
+                            "train_step_ring")
             optimizer.first_step = False
             return lo[0]
         if self._ddp.fused:
             x = self._check_inputs(x, target)
-            return self._ddp.fused_train_step(x, target, optimizer, loss_out)
+            return self._ddp.fused_train_step(x, target, optimizer, loss_out, ring)
+        if ring is not None:
+            raise RuntimeError("a resident input ring needs the single-process or the fused DDP step")
         loss = self.forward_backward(x, target, loss_out=loss_out)
         self._ddp.reduce_gradients()
         optimizer.step()
@@ -279,7 +325,7 @@ class StepGraph:
     Static input buffers ``x``/``target`` are filled by the caller (e.g. an H2D copy) before
     ``replay()``; ``loss`` is a 0-d view of the device scalar the graph writes."""
 
-    def __init__(self, model: Net, optimizer, batch: int, x=None, target=None, loss_out=None, loss_host=None):
+    def __init__(self, model: Net, optimizer, batch: int, x=None, target=None, loss_out=None, loss_host=None, ring=None):
         if optimizer.first_step:
             raise RuntimeError("run one eager step first (the first SGD step initialises the momentum buffer)")
         model = getattr(model, "module", model)  # accept our DistributedDataParallel wrapper
@@ -295,12 +341,18 @@ class StepGraph:
         side.wait_stream(torch.cuda.current_stream())
         # Warm-up on the capture stream (lazy CUDA/NCCL initialisation must happen outside the
         # capture); it is a real step on zero data, so the training state is put back afterwards.
+        # With ``ring`` (an InputRing) every replay reads the ring slot under the ring's device cursor and advances
+        # it: no input has to be staged between replays (x / target then receive a copy of the batch).
+        self.ring = ring
         saved = [t.clone() for t in (model.flat_params, model.flat_grads, model.flat_momentum)]
+        if ring is not None:
+            saved.append(ring.cursor.clone())
         with torch.cuda.stream(side):
-            model.train_step(self.x, self.target, optimizer, loss_out=loss_out)
+            model.train_step(self.x, self.target, optimizer, loss_out=loss_out, ring=ring)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize(dev)
-        for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum), saved):
+        for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum) + ((ring.cursor,) if ring is not None else ()),
+                         saved):
             t.copy_(sv)
         torch.cuda.synchronize(dev)
         # Under the fused DDP exchange a step writes its gradient into staging bucket (step & 1): the kernel
@@ -316,7 +368,7 @@ class StepGraph:
                 # thread_local: the NCCL watchdog thread may query its own events while this thread captures
                 # (in the default global mode that query invalidates the capture and the ranks dead-lock)
                 with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
-                    self.loss = model.train_step(self.x, self.target, optimizer, loss_out=loss_out)
+                    self.loss = model.train_step(self.x, self.target, optimizer, loss_out=loss_out, ring=ring)
                     if loss_host is not None:  # D2H memcpy node: every replay leaves the step's loss in pinned host memory
                         loss_host.copy_(self.loss.reshape(1), non_blocking=True)
             finally:

@@ -72,7 +72,7 @@ def fixture_run(dev, fused, graph):
     model.close()
 
 
-def property_run(dev, fused, graph=False, steps=6):
+def property_run(dev, fused, graph=False, steps=6, ring=False):
     rank, ws = dist.get_rank(), dist.get_world_size()
     torch.manual_seed(1)
     net = pkg.Net().to(dev)
@@ -94,9 +94,12 @@ def property_run(dev, fused, graph=False, steps=6):
         for r in range(1, ws):
             want += gathered[r]                        # rank order, like the fused kernels
         if graph and s > 0:
-            g = g or pkg.StepGraph(model, opt, 64)
-            g.x.copy_(x)
-            g.target.copy_(t)
+            if g is None:   # ring=True: the replays read this rank's batch from a one-slot resident ring instead
+                in_ring = pkg.InputRing(64, x=x[None].clone(), target=t[None].clone()) if ring else None
+                g = pkg.StepGraph(model, opt, 64, ring=in_ring)
+            if not ring:
+                g.x.copy_(x)
+                g.target.copy_(t)
             losses.append(float(g.replay()))
         else:
             losses.append(float(model.train_step(x, t, opt)))
@@ -170,7 +173,8 @@ def main():
     if mode == "soak":
         soak_run(dev)
     elif mode.startswith("prop"):
-        property_run(dev, fused=mode.startswith("prop-fused"), graph=mode.endswith("graph"))
+        property_run(dev, fused=mode.startswith("prop-fused"), graph=mode.endswith("graph") or mode.endswith("ring"),
+                     ring=mode.endswith("ring"))
     else:
         fixture_run(dev, fused=mode.startswith("fused"), graph=mode.endswith("graph"))
     smoke_dist_run()

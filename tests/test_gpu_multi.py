@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WORKER = os.path.join(ROOT, "tests", "ddp_worker.py")
 MODES = ["eager", "graph", "fused", "fused-graph"]
-PROPS = ["prop-nccl", "prop-fused", "prop-fused-graph"]
+PROPS = ["prop-nccl", "prop-fused", "prop-fused-graph", "prop-fused-ring"]
 
 
 def _need(n):
@@ -52,7 +52,7 @@ def test_ddp_many_gpus_properties(world, mode):
     """BASELINE configs 3/4 at N=2/4/8: rank-ordered gradient sum, bit-identical replicas, decreasing loss, smoke-dist
     send/recv and all_reduce bit-exactness."""
     _need(world)
-    rc = launcher.launch([WORKER, mode], workers=world - 1, port=23470 + 3 * world + PROPS.index(mode), timeout=240)
+    rc = launcher.launch([WORKER, mode], workers=world - 1, port=23470 + 4 * world + PROPS.index(mode), timeout=240)
     assert rc == 0
 
 

@@ -83,6 +83,54 @@ def test_step_pipeline_matches_eager_steps():
     assert l_e == l_p and torch.equal(p_e, p_p)  # same kernels, same order: bit-identical
 
 
+@pytest.mark.parametrize("packed", [True, False])
+def test_resident_input_ring_steps_match_plain_steps(packed):
+    """b200mnist_train_step_ring: batches resident in a device ring, read through a device-side cursor (eager and as
+    CUDA-graph replays with no copy in between) give bit-identical training to the same batches passed one by one;
+    the cursor wraps, and x / target receive the slot's batch."""
+    import pytorch_operator_b200 as pkg
+    B, slots, steps = 64, 3, 8
+    batches = [mo.synthetic_batch(B, 700 + i) for i in range(slots)]
+
+    def plain():
+        torch.manual_seed(1)
+        net = pkg.Net().to(DEV)
+        opt = pkg.SGD(net.parameters(), lr=0.01, momentum=0.5)
+        losses = [float(net.train_step(batches[i % slots][0].to(DEV), batches[i % slots][1].to(DEV), opt)) for i in range(steps)]
+        return losses, net.flat_params.clone()
+
+    def ringed():
+        torch.manual_seed(1)
+        net = pkg.Net().to(DEV)
+        opt = pkg.SGD(net.parameters(), lr=0.01, momentum=0.5)
+        if packed:
+            rec = torch.empty(slots, B * 784 * 4 + B * 8, dtype=torch.uint8, device=DEV)
+            for i, (x, t) in enumerate(batches):
+                rec[i, :B * 784 * 4].view(torch.float32).copy_(x.reshape(-1))
+                rec[i, B * 784 * 4:].view(torch.int64).copy_(t)
+            ring = pkg.InputRing(B, records=rec)
+        else:
+            ring = pkg.InputRing(B, x=torch.stack([b[0] for b in batches]).to(DEV), target=torch.stack([b[1] for b in batches]).to(DEV))
+        x = torch.zeros(B, 1, 28, 28, device=DEV)
+        t = torch.zeros(B, dtype=torch.int64, device=DEV)
+        losses = [float(net.train_step(x, t, opt, ring=ring)) for _ in range(2)]        # eager: slots 0, 1
+        assert int(ring.cursor) == 2 and torch.equal(x.cpu(), batches[1][0]) and torch.equal(t.cpu(), batches[1][1])
+        g = pkg.StepGraph(net, opt, B, x=x, target=t, ring=ring)                         # warm-up leaves the cursor alone
+        assert int(ring.cursor) == 2
+        for i in range(2, steps):
+            losses.append(float(g.replay()))
+            assert int(ring.cursor) == (i + 1) % slots
+        assert torch.equal(x.cpu(), batches[(steps - 1) % slots][0])
+        return losses, net.flat_params.clone()
+
+    (l_p, p_p), (l_r, p_r) = plain(), ringed()
+    assert l_p == l_r and torch.equal(p_p, p_r)
+    ring = pkg.InputRing(B, x=torch.zeros(2, B, 1, 28, 28, device=DEV), target=torch.zeros(2, B, dtype=torch.int64, device=DEV))
+    with pytest.raises(ValueError):
+        pkg.Net().to(DEV).train_step(torch.zeros(8, 1, 28, 28, device=DEV), torch.zeros(8, dtype=torch.int64, device=DEV),
+                                     None, ring=ring)
+
+
 def test_launcher_runs_single_replica_job():
     from pytorch_operator_b200 import launcher
     rc = launcher.launch(["-m", "pytorch_operator_b200.mnist", "--synthetic", "3", "--test-batch-size", "100",
