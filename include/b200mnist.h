@@ -82,18 +82,30 @@ int b200mnist_train_step(float *params, float *grads, float *momentum, const flo
 /* "Resident input": the batches of many steps already sit in device memory (a ring of slots) and the step picks its
  * own -- for training loops that replay one CUDA graph per step with no copy and no host-side pointer in between
  * (replaces the DataLoader + `data.to(device)` of mnist.py:37-38 when the data fits in HBM).
- *   slot s: images at x + s * x_stride floats ([B,1,28,28] fp32, 16-byte aligned), targets at target + s * t_stride
- *   cursor: one uint32 in DEVICE memory: the slot the next step reads.  conv1's forward kernel reads it, the step's
- *           last kernel sets it to (cursor + 1) % slots.  The host may rewrite it between steps (stream-ordered).
+ *   slot s : images at x + s * x_stride floats ([B,1,28,28] fp32, 16-byte aligned), targets at target + s * t_stride
+ *   state  : two uint32 in DEVICE memory (8-byte aligned, zero-filled once): [0] the cursor -- the slot the next step
+ *            reads -- and [1] the number of steps that have consumed the ring.  conv1's forward kernel reads them, the
+ *            step's last kernel sets them to (cursor + 1) % slots and steps + 1.  The host may rewrite the cursor
+ *            between steps (stream-ordered).
  * b200mnist_train_step_ring is b200mnist_train_step reading its batch from the ring: `x` and `target` are now OUTPUT
  * buffers of the step ([B,1,28,28] fp32 and int64[B]): the first kernel leaves the slot's batch there for the rest
- * of the step (and for the caller to inspect).  ring_host is read during the call only. */
+ * of the step (and for the caller to inspect).  ring_host is read during the call only.
+ * Host-fed ring (optional members, NULL for a ring that is simply resident): a copy stream refills the slots while
+ * the steps run, and the compute stream carries nothing but the step launches --
+ *   landed      : DEVICE uint32: sequence number (1, 2, ...) of the newest batch that has arrived in the ring, written
+ *                 BEHIND each copy in copy-stream order (b200mnist_stage_record).  Step n waits on the device until
+ *                 landed >= n.
+ *   report_host : uint64[slots] in PINNED HOST memory: the last kernel of step n stores (n << 32 | bits of the loss)
+ *                 into report_host[slot of step n] as one 8-byte word: when the high half reads n, step n is done, its
+ *                 loss is the low half, and the slot may be refilled. */
 typedef struct b200mnist_ring {
     const float *x;
     const int64_t *target;
     int64_t x_stride, t_stride;
     uint32_t slots;
-    uint32_t *cursor;
+    uint32_t *state;
+    const uint32_t *landed;
+    uint64_t *report_host;
 } b200mnist_ring_t;
 int b200mnist_train_step_ring(float *params, float *grads, float *momentum, const b200mnist_ring_t *ring_host, float *x,
                               int64_t *target, int B, void *workspace, int64_t workspace_bytes, float lr, float mu,
@@ -260,6 +272,11 @@ int b200mnist_square(const float *in, float *out, int64_t n, void *stream);
 int b200mnist_stage_inputs(void *dst_device, const void *src_host_pinned, int64_t bytes, void *copy_stream,
                            void *compute_stream, void *ev_slot_free, void *ev_copied);
 int b200mnist_event_record(void *event, void *stream);
+/* Refill of a host-fed ring slot (see b200mnist_ring_t): cudaMemcpyAsync of `bytes` from pinned host (or device) memory
+ * to dst_device on copy_stream and, if landed_word is not NULL, a stream-ordered 32-bit write of `seq` to that DEVICE
+ * word behind it (cuStreamWriteValue32): no kernel, no event, nothing on the compute stream. */
+int b200mnist_stage_record(void *dst_device, const void *src, int64_t bytes, void *copy_stream, uint32_t *landed_word,
+                           uint32_t seq);
 
 /* ---- instrumentation for bench.py (no counterpart in the reference) ----------------
  * b200mnist_launch_count: kernels this library has launched in this process so far.

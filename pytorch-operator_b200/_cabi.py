@@ -105,6 +105,7 @@ SIGNATURES = {
     "b200mnist_square": (_i32, [_c_f, _c_f, _i64, _c_f]),
     "b200mnist_stage_inputs": (_i32, [_c_f, _c_f, _i64, _c_f, _c_f, _c_f, _c_f]),
     "b200mnist_event_record": (_i32, [_c_f, _c_f]),
+    "b200mnist_stage_record": (_i32, [_c_f, _c_f, _i64, _c_f, _c_f, ctypes.c_uint32]),
     "b200mnist_launch_count": (ctypes.c_longlong, []),
     "b200mnist_delay": (_i32, [_c_f, _i32]),
     "b200mnist_fma_peak": (_i64, [_c_f, _i32, _i32, _c_f]),
@@ -117,7 +118,8 @@ SIGNATURES = {
 class Ring(ctypes.Structure):
     """b200mnist_ring_t (include/b200mnist.h)."""
     _fields_ = [("x", ctypes.c_void_p), ("target", ctypes.c_void_p), ("x_stride", ctypes.c_int64),
-                ("t_stride", ctypes.c_int64), ("slots", ctypes.c_uint32), ("cursor", ctypes.c_void_p)]
+                ("t_stride", ctypes.c_int64), ("slots", ctypes.c_uint32), ("state", ctypes.c_void_p),
+                ("landed", ctypes.c_void_p), ("report_host", ctypes.c_void_p)]
 
 
 _lib = None

@@ -244,19 +244,30 @@ int launch_conv1_fwd(const float *x, const float *w, const float *b, float *out,
 // Validates a caller's ring description (include/b200mnist.h) and turns it into the kernels' RingRef; x / target are the
 // step's ordinary input buffers, which conv1's forward kernel fills from the ring.
 int make_ring(const b200mnist_ring_t *ring, const float *x, const int64_t *target, int B, RingRef *out) {
-    if (!ring->x || !ring->target || !ring->cursor) return fail_arg(1, "null pointer in the ring description");
+    if (!ring->x || !ring->target || !ring->state) return fail_arg(1, "null pointer in the ring description");
     if (ring->slots < 1) return fail_arg(2, "the ring needs at least one slot");
-    if (!aligned16(ring->x) || ((ring->x_stride * 4) & 15) || ring->x_stride < (int64_t)B * kXElems || ring->t_stride < B)
-        return fail_arg(3, "ring slots must be 16-byte aligned and at least one batch apart");
+    if (!aligned16(ring->x) || ((ring->x_stride * 4) & 15) || ring->x_stride < (int64_t)B * kXElems || ring->t_stride < B ||
+        (reinterpret_cast<uintptr_t>(ring->state) & 7u))
+        return fail_arg(3, "ring slots must be 16-byte aligned and at least one batch apart, `state` 8-byte aligned");
     out->x = ring->x;
     out->target = reinterpret_cast<const long long *>(ring->target);
     out->x_stride = ring->x_stride;
     out->t_stride = ring->t_stride;
     out->x_copy = const_cast<float *>(x);
     out->t_copy = reinterpret_cast<long long *>(const_cast<int64_t *>(target));
-    out->cursor = ring->cursor;
+    out->state = ring->state;
+    out->landed = ring->landed;
     out->slots = ring->slots;
     return 0;
+}
+LossReduce ring_loss_reduce(const float *rows, float *loss_out, int B, const b200mnist_ring_t *ring) {
+    LossReduce l{rows, loss_out, B, 1.0f / (float)B, nullptr, 0u, nullptr};
+    if (ring) {
+        l.state = ring->state;
+        l.slots = ring->slots;
+        l.report_host = reinterpret_cast<unsigned long long *>(ring->report_host);
+    }
+    return l;
 }
 const char *kTmapErr = "cuTensorMapEncodeTiled failed or is unavailable (driver too old?)";
 // conv2 forward on the tensor cores (tcgen05 3xTF32, shifted-window implicit GEMM; tc_conv.cuh).  `w2s` receives the
@@ -684,7 +695,7 @@ int train_step_impl(float *params, float *grads, float *momentum, const float *x
                           ring ? &rr : nullptr)))
         return rc;
     const GradSegments segs = step_segments(w, pl);
-    LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B, ring ? rr.cursor : nullptr, ring ? rr.slots : 0u};
+    const LossReduce lrd = ring_loss_reduce(w.rows, loss_out, B, ring);
     return launch_sgd_fused(params, grads, momentum, lr, mu, 1.0f, first_step, segs, lrd, s);
 }
 }  // namespace
@@ -827,7 +838,7 @@ int peer_train_step_impl(void *const *windows_host, int rank, int world_size, in
                           ring ? &rr : nullptr)))
         return rc;
     const GradSegments segs = step_segments(w, pl);
-    const LossReduce lrd{w.rows, loss_out, B, 1.0f / (float)B, ring ? rr.cursor : nullptr, ring ? rr.slots : 0u};
+    const LossReduce lrd = ring_loss_reduce(w.rows, loss_out, B, ring);
     switch (world_size) {
     case 2: return launch_peer_tail<2>(ps, segs, lrd, s);
     case 4: return launch_peer_tail<4>(ps, segs, lrd, s);
@@ -1092,6 +1103,27 @@ int b200mnist_stage_inputs(void *dst_device, const void *src_host_pinned, int64_
     if (e == cudaSuccess) e = cudaEventRecord(static_cast<cudaEvent_t>(ev_copied), cs);
     if (e == cudaSuccess) e = cudaStreamWaitEvent(ms, static_cast<cudaEvent_t>(ev_copied), 0);
     if (e != cudaSuccess) return fail_cuda(e, "stage_inputs");
+    return 0;
+}
+int b200mnist_stage_record(void *dst_device, const void *src, int64_t bytes, void *copy_stream, uint32_t *ready_word,
+                           uint32_t seq) {
+    if (!dst_device || !src || bytes <= 0) return fail_arg(1, "null pointer argument");
+    cudaStream_t cs = static_cast<cudaStream_t>(copy_stream);
+    cudaError_t e = cudaMemcpyAsync(dst_device, src, (size_t)bytes, cudaMemcpyDefault, cs);
+    if (e != cudaSuccess) return fail_cuda(e, "stage_record: cudaMemcpyAsync");
+    if (!ready_word) return 0;
+    typedef CUresult (*WriteValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+    static WriteValue32Fn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return fail_arg(8, "cuStreamWriteValue32 is unavailable (driver too old?)");
+        fn = reinterpret_cast<WriteValue32Fn>(p);
+    }
+    const CUresult r = fn(reinterpret_cast<CUstream>(cs), reinterpret_cast<CUdeviceptr>(ready_word), seq, 0);
+    if (r != CUDA_SUCCESS) return fail_arg(8, "cuStreamWriteValue32 failed");
     return 0;
 }
 int b200mnist_event_record(void *event, void *stream) {

@@ -61,14 +61,30 @@ __device__ __forceinline__ void send_early_signal(const EarlySignal &sig) {
 // CUDA-graph replay of the step needs no copy and no host-side pointer: conv1's forward kernel reads slot *cursor
 // (x + slot * x_stride floats, target + slot * t_stride elements), leaves copies in the step's ordinary input buffers
 // (x_copy / t_copy: what the later kernels of the step read) and the step's last kernel advances the cursor.
+// Host-fed rings (a copy stream refills the slots while the steps run): `landed` holds the sequence number of the
+// newest batch that has arrived (written behind each copy, in copy-stream order) and state[1] counts the steps that
+// have consumed the ring, so step n (1-based) waits until landed >= n -- on the device, which is what lets the
+// compute stream carry nothing but the graph launches.  nullptr for a ring that is simply resident.
 struct RingRef {
     const float *x;
     const long long *target;
     long long x_stride, t_stride;
     float *x_copy;
     long long *t_copy;
-    unsigned *cursor;
+    unsigned *state;          // [0] cursor: the slot the next step reads; [1] steps done (8-byte aligned pair)
+    const unsigned *landed;
     unsigned slots;
+};
+struct SpinClock {   // wall-clock bound for a spin loop: a producer that never arrives must not hang this GPU
+    unsigned long long t0 = 0;
+    unsigned n = 0;
+    __device__ __forceinline__ void tick() {
+        if ((++n & 1023u) == 0u) {
+            const unsigned long long now = global_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > kSpinTimeoutNs) __trap();
+        }
+    }
 };
 
 __device__ __forceinline__ float warp_sum(float v) {

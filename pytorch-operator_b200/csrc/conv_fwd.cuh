@@ -110,7 +110,16 @@ __global__ void __launch_bounds__(kC1Threads)
 conv1_relu_pool_fwd_ring_kernel(const RingRef r, const float *__restrict__ w, const float *__restrict__ bias,
                                 float *__restrict__ out, uint8_t *__restrict__ idx, int B) {
     pdl_wait();
-    const unsigned slot = *reinterpret_cast<const volatile unsigned *>(r.cursor);
+    uint2 st;   // {cursor, steps done}: one 8-byte load, straight from L2
+    asm volatile("ld.global.cg.v2.u32 {%0, %1}, [%2];" : "=r"(st.x), "=r"(st.y) : "l"(r.state));
+    const unsigned slot = st.x;
+    if (r.landed) {   // host-fed ring: the batch of this step may still be on its way (normally it landed long ago)
+        if (threadIdx.x == 0) {
+            SpinClock clk;
+            while ((int)(ld_acquire_sys(r.landed) - (st.y + 1)) < 0) clk.tick();
+        }
+        __syncthreads();
+    }
     if (blockIdx.y == 0 && threadIdx.x == 0) r.t_copy[blockIdx.x] = r.target[(long long)slot * r.t_stride + blockIdx.x];
     conv1_fwd_body<true>(r.x + (long long)slot * r.x_stride, w, bias, out, idx, B, r.x_copy);
 }

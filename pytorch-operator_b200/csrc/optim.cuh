@@ -52,13 +52,25 @@ struct LossReduce {   // rows == nullptr: nothing to do
     float *out;
     int B;
     float scale;
-    unsigned *cursor;   // resident-input steps (RingRef): the block that reduces the loss also advances the ring cursor
+    // resident-input steps (RingRef): the block that reduces the loss also closes the step on the ring
+    unsigned *state;                    // [0] cursor -> next slot, [1] steps done + 1
     unsigned slots;
+    unsigned long long *report_host;    // host-fed rings: report_host[slot] (PINNED HOST memory) = {step number, loss bits}
 };
-__device__ __forceinline__ void advance_cursor(const LossReduce &lr) {
-    if (lr.cursor && threadIdx.x == 0) {
-        const unsigned c = *lr.cursor + 1;
-        *lr.cursor = c >= lr.slots ? 0u : c;
+// Last block of the step's last kernel: the scalar loss, then the ring bookkeeping.  The report to the host is ONE
+// 8-byte store (sequence number in the high word, the loss in the low one): the host sees both or neither, so no
+// system-scope fence has to order a "done" flag behind the loss at the very end of the step.
+__device__ __forceinline__ void finish_step(const LossReduce &lr) {
+    if (lr.rows) reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
+    if (lr.state && threadIdx.x == 0) {
+        const unsigned slot = lr.state[0], done = lr.state[1] + 1;
+        lr.state[0] = slot + 1 >= lr.slots ? 0u : slot + 1;
+        lr.state[1] = done;
+        if (lr.report_host) {
+            const float loss = lr.rows ? *reinterpret_cast<volatile float *>(lr.out) : 0.f;   // written by this thread above
+            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(lr.report_host + slot),
+                         "l"(((unsigned long long)done << 32) | (unsigned long long)__float_as_uint(loss)) : "memory");
+        }
     }
 }
 
@@ -180,8 +192,7 @@ sgd_fused_kernel(float *__restrict__ p, float *__restrict__ g, float *__restrict
         *reinterpret_cast<float4 *>(m + i4) = make_float4(ms[0], ms[1], ms[2], ms[3]);
         *reinterpret_cast<float4 *>(p + i4) = make_float4(ps[0], ps[1], ps[2], ps[3]);
     } else {
-        if (lr.rows) reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
-        advance_cursor(lr);
+        finish_step(lr);
     }
 }
 

@@ -80,17 +80,6 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned 
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-struct SpinClock {   // wall-clock bound for a spin loop: a peer that never arrives (crashed rank) must not hang this GPU
-    unsigned long long t0 = 0;
-    unsigned n = 0;
-    __device__ __forceinline__ void tick() {
-        if ((++n & 1023u) == 0u) {
-            const unsigned long long now = global_ns();
-            if (t0 == 0) t0 = now;
-            else if (now - t0 > kSpinTimeoutNs) __trap();
-        }
-    }
-};
 // wait until *p has reached `want` (epochs only grow; signed difference is wrap-safe)
 __device__ __forceinline__ void spin_until(const unsigned *p, unsigned want) {
     SpinClock clk;
@@ -216,8 +205,7 @@ peer_tail_kernel(const __grid_constant__ PeerWin pw, float *__restrict__ m, int 
         // the preceding grid has completed, so its stores into the peers' windows are ordered before these flags
         if (t < WORLD && t != rank) st_release_sys(win_flags(pw.base[t]) + kFlagFc1Pushed + rank, epoch);
         if (t == 0) flags[kFlagEpochA] = epoch;   // read by the next step's exchange CTAs
-        if (lr.rows) reduce_rows_block(lr.rows, lr.B, lr.scale, 0, lr.out);
-        advance_cursor(lr);
+        finish_step(lr);
         // the step is over when every peer's fc1 slice has landed in this rank's window as well
         if (t < WORLD && t != rank) spin_until(flags + kFlagFc1Pushed + t, epoch);
         return;

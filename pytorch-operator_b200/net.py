@@ -44,17 +44,19 @@ class InputRing:
     of CUDA-graph replays needs no per-step copy and no host-side pointer (what the reference does with a DataLoader
     and ``data.to(device)``, mnist.py:37-38, when the data fits in HBM).
 
-    ``records``: uint8 [slots, B*784*4 + B*8], each row one packed batch (fp32 images, then int64 targets) -- or pass
-    ``x`` [slots,B,1,28,28] float32 and ``target`` [slots,B] int64."""
+    ``records``: uint8 [slots, row] with row >= B*784*4 + B*8 and a multiple of 16: each row one packed batch (fp32
+    images, then int64 targets) -- or pass ``x`` [slots,B,1,28,28] float32 and ``target`` [slots,B] int64.
+    ``host_fed``: the slots are refilled by a copy stream while the steps run (``StepPipeline``): adds the per-slot
+    ``ready`` sequence numbers the steps wait on, the ``steps_done`` counter and its pinned-host mirror."""
 
-    def __init__(self, batch, records=None, x=None, target=None):
+    def __init__(self, batch, records=None, x=None, target=None, host_fed=False):
         import ctypes
         self.batch = batch
         if records is not None:
             xb = batch * 784 * 4
-            if records.dtype != torch.uint8 or records.dim() != 2 or records.shape[1] != xb + batch * 8 \
+            if records.dtype != torch.uint8 or records.dim() != 2 or records.shape[1] < xb + batch * 8 \
                     or not records.is_contiguous() or records.shape[1] % 16:
-                raise ValueError("records must be contiguous uint8 [slots, B*784*4 + B*8] with 16-byte aligned rows")
+                raise ValueError("records must be contiguous uint8 [slots, >= B*784*4 + B*8] with rows a multiple of 16 bytes")
             self._keep = (records,)
             x_ptr, t_ptr = records.data_ptr(), records.data_ptr() + xb
             x_stride, t_stride, slots, dev = records.shape[1] // 4, records.shape[1] // 8, records.shape[0], records.device
@@ -65,14 +67,50 @@ class InputRing:
                 raise ValueError("x must be float32 [slots,B,1,28,28] and target int64 [slots,B], both contiguous")
             self._keep = (x, target)
             x_ptr, t_ptr, x_stride, t_stride, slots, dev = x.data_ptr(), target.data_ptr(), batch * 784, batch, x.shape[0], x.device
-        self.slots, self.device = slots, dev
-        self.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.desc = _cabi.Ring(x_ptr, t_ptr, x_stride, t_stride, slots, self.cursor.data_ptr())
+        self.slots, self.device, self.host_fed = slots, dev, host_fed
+        self.state = torch.zeros(2, dtype=torch.int32, device=dev)     # [cursor, steps done]
+        self.cursor = self.state[0:1]
+        self.landed = torch.zeros(1, dtype=torch.int32, device=dev) if host_fed else None
+        self.report_host = torch.zeros(slots, dtype=torch.int64).pin_memory() if host_fed else None
+        self.desc = _cabi.Ring(x_ptr, t_ptr, x_stride, t_stride, slots, self.state.data_ptr(),
+                               self.landed.data_ptr() if host_fed else None,
+                               self.report_host.data_ptr() if host_fed else None)
         self.desc_ptr = ctypes.addressof(self.desc)
+        self._report = (ctypes.c_uint64 * slots).from_address(self.report_host.data_ptr()) if host_fed else None
 
     def seek(self, slot: int):
         """Point the cursor at ``slot`` (stream-ordered)."""
         self.cursor.fill_(int(slot) % self.slots)
+
+    def report(self, step: int):
+        """Host-fed rings: (done, loss) of 0-based step ``step`` as last reported to pinned host memory by the step's
+        last kernel (one 8-byte word: no CUDA call, no tearing).  ``done`` turns True when the step has completed;
+        ``loss`` is None once the slot has been reused by a later step."""
+        word = self._report[step % self.slots]
+        seq = word >> 32
+        if seq < step + 1:
+            return False, None
+        if seq > step + 1:
+            return True, None
+        import struct
+        return True, struct.unpack("<f", struct.pack("<I", word & 0xFFFFFFFF))[0]
+
+    # a StepGraph runs one real step on the ring while warming up; these put the ring back exactly as it was
+    def _snapshot(self):
+        torch.cuda.synchronize(self.device)
+        snap = {"state": self.state.clone()}
+        if self.host_fed:
+            snap.update(landed=self.landed.clone(), report=self.report_host.clone())
+            self.landed.fill_(int(self.state[1]) + 1)    # let the warm-up step find "its" batch
+        return snap
+
+    def _restore(self, snap):
+        torch.cuda.synchronize(self.device)
+        self.state.copy_(snap["state"])
+        if self.host_fed:
+            self.landed.copy_(snap["landed"])
+            self.report_host.copy_(snap["report"])
+        torch.cuda.synchronize(self.device)
 
 
 class _Leaf(nn.Module):
@@ -345,15 +383,16 @@ class StepGraph:
         # it: no input has to be staged between replays (x / target then receive a copy of the batch).
         self.ring = ring
         saved = [t.clone() for t in (model.flat_params, model.flat_grads, model.flat_momentum)]
-        if ring is not None:
-            saved.append(ring.cursor.clone())
+        ring_snap = ring._snapshot() if ring is not None else None
+        side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             model.train_step(self.x, self.target, optimizer, loss_out=loss_out, ring=ring)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize(dev)
-        for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum) + ((ring.cursor,) if ring is not None else ()),
-                         saved):
+        for t, sv in zip((model.flat_params, model.flat_grads, model.flat_momentum), saved):
             t.copy_(sv)
+        if ring is not None:
+            ring._restore(ring_snap)
         torch.cuda.synchronize(dev)
         # Under the fused DDP exchange a step writes its gradient into staging bucket (step & 1): the kernel
         # arguments differ between even and odd steps, so both variants are captured and replay() alternates.
@@ -400,91 +439,94 @@ class StepGraph:
 class StepLoss:
     """What ``StepPipeline.submit`` returns: the loss of the step just enqueued.  The step's last kernel stores it
     in pinned host memory asynchronously, so reading it means waiting for THAT step -- ``item()`` (what
-    mnist.py:47 calls) and ``float()`` synchronise on the step's completion event first, like ``loss.item()`` on a
-    CUDA tensor does in the reference.  Read it before the same slot is submitted again (two steps later)."""
-    __slots__ = ("_pipe", "_slot")
+    mnist.py:47 calls) and ``float()`` wait until the step has reported completion to the host first, like
+    ``loss.item()`` on a CUDA tensor does in the reference.  Read it before ``slots`` more steps are submitted."""
+    __slots__ = ("_pipe", "_step")
 
-    def __init__(self, pipe, slot):
-        self._pipe, self._slot = pipe, slot
+    def __init__(self, pipe, step):
+        self._pipe, self._step = pipe, step
 
     def item(self) -> float:
-        self._pipe.ev_done[self._slot].synchronize()
-        return float(self._pipe.loss_host[self._slot])
+        self._pipe.wait_step(self._step)
+        loss = self._pipe.ring.report(self._step)[1]
+        if loss is None:
+            raise RuntimeError("this step's loss has been overwritten: read it before `slots` more steps are submitted")
+        return loss
 
     __float__ = item
 
 
 class StepPipeline:
-    """Double-buffered host-fed training: while step i runs (graph replay on the current stream),
-    the pinned host batch of step i+1 is copied to the other static input buffer on a copy stream;
-    each step's loss is written by the kernel directly into pinned host memory (``loss_host[slot]``).
+    """Host-fed training with nothing but graph launches on the compute stream.
+
+    The batches travel through a small ring of device slots (``InputRing(host_fed=True)``): ``submit`` copies the
+    pinned host batch of step n into slot n % slots on a COPY stream and writes the slot's sequence number behind the
+    copy (a stream memory operation, ``b200mnist_stage_record``), then replays the step's CUDA graph.  The step's
+    first kernel waits ON THE DEVICE until its slot carries its sequence number (normally it has for a long time: the
+    copies run ahead of the steps) and its last kernel stores the loss and the step count into pinned host memory,
+    (one 8-byte word), which is how the host knows a slot may be refilled and a loss may be read -- no event, no stream
+    wait, no copy node between two replays.
 
         pipe = StepPipeline(model, optimizer, batch)
         for rec in pinned_records:          # uint8 [batch*784*4 + batch*8]: fp32 images, then int64 targets
             loss = pipe.submit(rec)         # asynchronous; loss.item() waits for that step only
-        pipe.drain()                        # pipe.loss_host[k] holds the loss of the last step on slot k
+        pipe.drain()                        # pipe.loss_host[n % pipe.slots] holds the loss of step n (the last `slots` steps)
     """
 
-    def __init__(self, model, optimizer, batch: int):
+    def __init__(self, model, optimizer, batch: int, slots: int = 8):
         net = getattr(model, "module", model)
         dev = net.device
-        self.batch, self.xbytes, self.rec_bytes = batch, batch * 784 * 4, batch * 784 * 4 + batch * 8
-        self.slots = []
-        self.loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
-        for k in range(2):
-            packed = torch.zeros(self.rec_bytes, dtype=torch.uint8, device=dev)
-            x = packed[:self.xbytes].view(torch.float32).view(batch, 1, 28, 28)
-            t = packed[self.xbytes:].view(torch.int64)
-            # the step's last kernel stores the loss straight into pinned host memory (zero-copy over PCIe): the
-            # device->host transfer of the result costs no copy node and no extra launch
-            g = StepGraph(model, optimizer, batch, x=x, target=t, loss_out=self.loss_host[k:k + 1])
-            self.slots.append((packed, g))
+        self.batch, self.xbytes, self.rec_bytes, self.slots = batch, batch * 784 * 4, batch * 784 * 4 + batch * 8, slots
+        row = (self.rec_bytes + 15) // 16 * 16
+        self.records = torch.zeros(slots, row, dtype=torch.uint8, device=dev)
+        self.ring = InputRing(batch, records=self.records, host_fed=True)
+        self.x = torch.zeros(batch, 1, 28, 28, dtype=torch.float32, device=dev)     # the step's copy of its batch
+        self.target = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.graph = StepGraph(model, optimizer, batch, x=self.x, target=self.target, ring=self.ring)
         self.copy_stream = torch.cuda.Stream(device=dev)
-        self.ev_copied = [torch.cuda.Event(), torch.cuda.Event()]
-        self.ev_done = [torch.cuda.Event(), torch.cuda.Event()]
-        for e in self.ev_done + self.ev_copied:
-            e.record()                       # also creates the underlying cudaEvent_t handles
         self._lib = _cabi.lib()
+        self._keep = [None] * slots
         self.steps = 0
 
+    @property
+    def loss_host(self) -> torch.Tensor:
+        """The losses last reported per ring slot (float32 [slots]; slot = step % slots)."""
+        return (self.ring.report_host & 0xFFFFFFFF).to(torch.int32).view(torch.float32)
+
+    def wait_step(self, step: int):
+        """Block the host until step ``step`` (0-based) of this pipeline has completed (spins on pinned memory)."""
+        while not self.ring.report(step)[0]:
+            pass
+
     def submit(self, host_record, target=None):
-        """``host_record``: one packed uint8 record in pinned memory, or the image tensor when ``target`` is
-        given.  The packed form takes the fast path: the four stream operations are one C call."""
-        k = self.steps & 1
-        packed, g = self.slots[k]
-        main = torch.cuda.current_stream()
-        if target is None and host_record.is_pinned() and host_record.numel() == self.rec_bytes:
-            _cabi.check(self._lib.b200mnist_stage_inputs(packed.data_ptr(), host_record.data_ptr(), self.rec_bytes,
-                                                         self.copy_stream.cuda_stream, main.cuda_stream,
-                                                         self.ev_done[k].cuda_event, self.ev_copied[k].cuda_event),
-                        "stage_inputs")
-            g.replay()
-            _cabi.check(self._lib.b200mnist_event_record(self.ev_done[k].cuda_event, main.cuda_stream), "event_record")
-            self.steps += 1
-            return StepLoss(self, k)
-        if host_record.is_cuda:                             # already on the device (DeviceMNIST): plain D2D on the
-            if target is None:                              # compute stream, ordered after whatever produced it
-                packed.copy_(host_record, non_blocking=True)
-            else:
-                g.x.copy_(host_record, non_blocking=True)
-                g.target.copy_(target, non_blocking=True)
-            g.replay()
-            self.ev_done[k].record(main)
-            self.steps += 1
-            return StepLoss(self, k)
-        self.copy_stream.wait_event(self.ev_done[k])        # slot k's previous step has consumed its inputs
-        with torch.cuda.stream(self.copy_stream):           # H2D of this step's inputs, off the compute stream
-            if target is None:
-                packed.copy_(host_record, non_blocking=True)
-            else:
-                g.x.copy_(host_record, non_blocking=True)
-                g.target.copy_(target, non_blocking=True)
-            self.ev_copied[k].record(self.copy_stream)
-        main.wait_event(self.ev_copied[k])
-        g.replay()
-        self.ev_done[k].record(main)
+        """``host_record``: one packed uint8 record (fp32 images, then int64 targets), or the image tensor when
+        ``target`` is given; pinned host memory (copied while earlier steps run) or device memory."""
+        n = self.steps
+        slot, seq = n % self.slots, n + 1
+        if n >= self.slots:
+            self.wait_step(n - self.slots)          # the step that last read this slot is done
+        dst = self.records[slot].data_ptr()
+        cs = self.copy_stream.cuda_stream
+        ready = self.ring.landed.data_ptr()
+        if host_record.is_cuda or (target is not None and target.is_cuda):
+            # produced on the compute stream a moment ago (e.g. DeviceMNIST's gather kernel): the copy must follow it
+            self.copy_stream.wait_stream(torch.cuda.current_stream())
+        if target is None:
+            if host_record.numel() * host_record.element_size() != self.rec_bytes or not host_record.is_contiguous():
+                raise ValueError("a packed record is B*784*4 + B*8 contiguous bytes")
+            _cabi.check(self._lib.b200mnist_stage_record(dst, host_record.data_ptr(), self.rec_bytes, cs, ready, seq),
+                        "stage_record")
+        else:
+            if host_record.dtype != torch.float32 or target.dtype != torch.int64 or host_record.numel() != self.batch * 784 \
+                    or target.numel() != self.batch or not host_record.is_contiguous() or not target.is_contiguous():
+                raise ValueError("data must be contiguous float32 [B,1,28,28] and target int64 [B]")
+            _cabi.check(self._lib.b200mnist_stage_record(dst, host_record.data_ptr(), self.xbytes, cs, 0, 0), "stage_record")
+            _cabi.check(self._lib.b200mnist_stage_record(dst + self.xbytes, target.data_ptr(), self.batch * 8, cs, ready, seq),
+                        "stage_record")
+        self._keep[slot] = (host_record, target)        # the copy is asynchronous: keep the source alive until the slot is reused
+        self.graph.replay()
         self.steps += 1
-        return StepLoss(self, k)
+        return StepLoss(self, n)
 
     def drain(self):
         torch.cuda.current_stream().synchronize()
