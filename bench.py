@@ -366,8 +366,11 @@ class Bench:
         # NCCL DDP path, which has no ring form of the step, each batch is copied into the static buffer first.
         in_place = world == 1 or bool(getattr(model, "fused", False))
         in_ring = pkg.InputRing(B, records=ring) if in_place else None
-        graph = pkg.StepGraph(model, opt, B, x=sx, target=st, ring=in_ring)
-        for i in range(W):
+        # with the ring a graph may hold several consecutive steps (a graph boundary costs ~1.5 us of GPU time at
+        # B=64): the K timed steps are K / unroll replays
+        unroll = (4 if K % 4 == 0 else 2 if K % 2 == 0 else 1) if in_place else 1
+        graph = pkg.StepGraph(model, opt, B, x=sx, target=st, ring=in_ring, unroll=unroll)
+        for i in range((W + unroll - 1) // unroll):
             if not in_place:
                 static.copy_(ring[i % nring], non_blocking=True)
             graph.replay()
@@ -375,7 +378,7 @@ class Bench:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_start = time.time()
         e0.record()
-        for i in range(K):
+        for i in range(K // unroll):
             if not in_place:
                 static.copy_(ring[i % nring], non_blocking=True)
             graph.replay()
@@ -389,8 +392,8 @@ class Bench:
         # leg 2: end to end from pinned host memory, loss read back every step.  Public API:
         # StepPipeline.submit(pinned record) = H2D on a copy stream (double-buffered), graph replay, the loss stored
         # into pinned host memory by the step's last kernel -- all inside the timed region, every step.
-        pipe = pkg.StepPipeline(model, opt, B)
-        for i in range(W):
+        pipe = pkg.StepPipeline(model, opt, B, unroll=unroll)
+        for i in range((W + unroll - 1) // unroll * unroll):
             pipe.submit(host_ring[i % nhost])
         pipe.drain()
         self.barrier()
@@ -418,7 +421,7 @@ class Bench:
         del graph, pipe
         out = {"B": B, "K": K, "W": W, "rec": rec, "nring": nring, "ms_total": ms_total, "ms_e2e": ms_e2e,
                "kernels_per_step": kernels_per_step, "clocks": clocks, "clocks_e2e": clocks_e2e,
-               "loss_final": loss_final, "timeline": timeline}
+               "loss_final": loss_final, "timeline": timeline, "unroll": unroll}
         if rank != 0:
             return out
 
@@ -583,9 +586,10 @@ def main():
                    "parallelism": f"dp{world}", "l2": f"inputs cycle through {main_r['nring']} distinct device-resident "
                                                       f"batches ({main_r['nring'] * main_r['rec'] / 1e6:.0f} MB > 126 MB L2), "
                                                       "read in place through a device-side cursor",
-                   "cuda_graph": True, "lr": 0.01, "momentum": 0.5},
-        "e2e": dict(m["e2e"], how="StepPipeline.submit(pinned record): H2D on a copy stream into the idle one of two "
-                                  "static buffers, graph replay, the loss stored by the last kernel straight into pinned "
+                   "cuda_graph": True, "steps_per_graph": main_r["unroll"], "lr": 0.01, "momentum": 0.5},
+        "e2e": dict(m["e2e"], how="StepPipeline.submit(pinned record): H2D on a copy stream into a slot of a small device "
+                                  "ring with the slot's sequence number written behind it, graph replay (the step waits for "
+                                  "its slot on the device), {step, loss} stored by the last kernel straight into pinned "
                                   "host memory (zero-copy D2H) -- every step."),
         "gpu_launches": m["kernels_per_step"] * K, "kernels_per_step": m["kernels_per_step"],
         "clocks": m["clocks"], "clocks_e2e": m["clocks_e2e"], "roofline": m["roofline"],

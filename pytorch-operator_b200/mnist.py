@@ -53,9 +53,12 @@ def train(args, model, device, train_loader, optimizer, epoch, writer):
         B = len(data)
         g = graphs.get(B)
         if g is None and use_graph and not optimizer.first_step:
-            g = graphs[B] = StepPipeline(model, optimizer, B)
+            g = graphs[B] = StepPipeline(model, optimizer, B, unroll=4)
+        for other in graphs.values():   # steps run in submission order: a pipeline of another batch size launches first
+            if other is not g:
+                other.flush()
         if g is not None:
-            loss = g.submit(data, target)  # H2D on a copy stream, overlapped with the previous step
+            loss = g.submit(data, target)  # H2D on a copy stream, overlapped with the previous steps
         else:
             data, target = data.to(device, non_blocking=True), target.to(device, non_blocking=True)
             loss = model.train_step(data, target, optimizer)
@@ -65,6 +68,8 @@ def train(args, model, device, train_loader, optimizer, epoch, writer):
                 100. * batch_idx / len(train_loader), loss.item()))
             niter = epoch * len(train_loader) + batch_idx
             writer.add_scalar('loss', loss.item(), niter)
+    for g in graphs.values():
+        g.flush()
 
 
 def test(args, model, device, test_loader, writer, epoch):

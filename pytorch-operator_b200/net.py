@@ -361,11 +361,17 @@ class StepGraph:
     """The fused training step captured once in a CUDA graph and replayed per batch
     (the B=64 step is launch-latency bound: ~10 kernels of a few microseconds each).
     Static input buffers ``x``/``target`` are filled by the caller (e.g. an H2D copy) before
-    ``replay()``; ``loss`` is a 0-d view of the device scalar the graph writes."""
+    ``replay()``; ``loss`` is a 0-d view of the device scalar the graph writes.  With an ``InputRing`` a graph may
+    hold ``unroll`` consecutive steps (each reads the slot under the ring's device cursor): one ``replay()`` is then
+    ``unroll`` steps, and the ~1.5 us a graph boundary costs on the GPU is paid once per ``unroll`` steps."""
 
-    def __init__(self, model: Net, optimizer, batch: int, x=None, target=None, loss_out=None, loss_host=None, ring=None):
+    def __init__(self, model: Net, optimizer, batch: int, x=None, target=None, loss_out=None, loss_host=None, ring=None,
+                 unroll: int = 1):
         if optimizer.first_step:
             raise RuntimeError("run one eager step first (the first SGD step initialises the momentum buffer)")
+        if unroll < 1 or (unroll > 1 and ring is None):
+            raise ValueError("unroll > 1 needs an InputRing (each of the graph's steps reads its own slot)")
+        self.unroll = unroll
         model = getattr(model, "module", model)  # accept our DistributedDataParallel wrapper
         dev = model.device
         self.model, self.optimizer = model, optimizer
@@ -407,7 +413,10 @@ class StepGraph:
                 # thread_local: the NCCL watchdog thread may query its own events while this thread captures
                 # (in the default global mode that query invalidates the capture and the ranks dead-lock)
                 with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
-                    self.loss = model.train_step(self.x, self.target, optimizer, loss_out=loss_out, ring=ring)
+                    for u in range(unroll):   # `unroll` consecutive steps per replay: one graph boundary per `unroll` steps
+                        if self._ddp is not None:
+                            self._ddp._force_parity = (variant + u) & 1
+                        self.loss = model.train_step(self.x, self.target, optimizer, loss_out=loss_out, ring=ring)
                     if loss_host is not None:  # D2H memcpy node: every replay leaves the step's loss in pinned host memory
                         loss_host.copy_(self.loss.reshape(1), non_blocking=True)
             finally:
@@ -429,7 +438,7 @@ class StepGraph:
             raise RuntimeError("lr/momentum changed after capture; build a new StepGraph")
         if self._ddp is not None:
             variant = self._ddp._step & 1
-            self._ddp._step += 1
+            self._ddp._step += self.unroll
         else:
             variant = 0
         self.graphs[variant].replay()
@@ -473,7 +482,9 @@ class StepPipeline:
         pipe.drain()                        # pipe.loss_host[n % pipe.slots] holds the loss of step n (the last `slots` steps)
     """
 
-    def __init__(self, model, optimizer, batch: int, slots: int = 8):
+    def __init__(self, model, optimizer, batch: int, slots: int = 8, unroll: int = 1):
+        if unroll < 1 or 2 * unroll > slots:
+            raise ValueError("unroll must be at least 1 and at most slots / 2 (the copies have to run ahead of the steps)")
         net = getattr(model, "module", model)
         dev = net.device
         self.batch, self.xbytes, self.rec_bytes, self.slots = batch, batch * 784 * 4, batch * 784 * 4 + batch * 8, slots
@@ -483,6 +494,11 @@ class StepPipeline:
         self.x = torch.zeros(batch, 1, 28, 28, dtype=torch.float32, device=dev)     # the step's copy of its batch
         self.target = torch.zeros(batch, dtype=torch.int64, device=dev)
         self.graph = StepGraph(model, optimizer, batch, x=self.x, target=self.target, ring=self.ring)
+        # `unroll` > 1: the steps are launched `unroll` at a time (one graph holding that many steps); a step somebody
+        # waits for before its group is full goes out through the single-step graph
+        self.unroll, self._staged = unroll, 0
+        self.graph_n = (StepGraph(model, optimizer, batch, x=self.x, target=self.target, ring=self.ring, unroll=unroll)
+                        if unroll > 1 else None)
         self.copy_stream = torch.cuda.Stream(device=dev)
         self._lib = _cabi.lib()
         self._keep = [None] * slots
@@ -495,8 +511,17 @@ class StepPipeline:
 
     def wait_step(self, step: int):
         """Block the host until step ``step`` (0-based) of this pipeline has completed (spins on pinned memory)."""
+        if step >= self.steps - self._staged:
+            self.flush()
         while not self.ring.report(step)[0]:
             pass
+
+    def flush(self):
+        """Launch the steps that were submitted but are still waiting for their group of ``unroll`` to fill (call it
+        before anything else uses the model: another pipeline, an eager step, evaluation)."""
+        while self._staged:
+            self.graph.replay()
+            self._staged -= 1
 
     def submit(self, host_record, target=None):
         """``host_record``: one packed uint8 record (fp32 images, then int64 targets), or the image tensor when
@@ -524,10 +549,14 @@ class StepPipeline:
             _cabi.check(self._lib.b200mnist_stage_record(dst + self.xbytes, target.data_ptr(), self.batch * 8, cs, ready, seq),
                         "stage_record")
         self._keep[slot] = (host_record, target)        # the copy is asynchronous: keep the source alive until the slot is reused
-        self.graph.replay()
         self.steps += 1
+        self._staged += 1
+        if self._staged == self.unroll:
+            (self.graph_n or self.graph).replay()
+            self._staged = 0
         return StepLoss(self, n)
 
     def drain(self):
+        self.flush()
         torch.cuda.current_stream().synchronize()
         self.copy_stream.synchronize()

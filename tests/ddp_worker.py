@@ -118,8 +118,8 @@ def property_run(dev, fused, graph=False, steps=6, ring=False):
 
 
 def soak_run(dev, steps=400):
-    """world_size 2 only: `steps` CUDA-graph replays on the fused path against the same steps on the NCCL path, bit for
-    bit.  With two ranks every summation order gives the same bits (a + b), the SGD kernels round identically, so the
+    """world_size 2 only: `steps` CUDA-graph steps on the fused path (resident input ring, four steps per graph)
+    against the same steps on the NCCL path (one step per graph, batches copied in), bit for bit.  With two ranks every summation order gives the same bits (a + b), the SGD kernels round identically, so the
     two trajectories must stay IDENTICAL -- any race in the fused exchange (a flag seen before its data, a staging
     bucket or receive slot reused too early, a stale parameter slice) shows up as a differing bit within a few steps."""
     rank, ws = dist.get_rank(), dist.get_world_size()
@@ -134,14 +134,28 @@ def soak_run(dev, steps=400):
         assert model.fused == fused, model.fused_error
         opt = pkg.SGD(model.parameters(), lr=0.01, momentum=0.5)
         model.train_step(*batches[0], opt)
-        g = pkg.StepGraph(model, opt, 64)
         losses = []
-        for i in range(1, steps):
-            g.x.copy_(batches[i % 8][0], non_blocking=True)
-            g.target.copy_(batches[i % 8][1], non_blocking=True)
-            g.replay()
-            if i % 50 == 0:
-                losses.append(float(g.loss))
+        if fused:
+            # the fused run reads its batches from a resident ring, four steps per graph launch (the staging parity
+            # alternates inside the graph); the last three steps go out one by one
+            order = [batches[(j + 1) % 8] for j in range(8)]
+            ring = pkg.InputRing(64, x=torch.stack([b[0] for b in order]), target=torch.stack([b[1] for b in order]))
+            g4 = pkg.StepGraph(model, opt, 64, ring=ring, unroll=4)
+            g1 = pkg.StepGraph(model, opt, 64, x=g4.x, target=g4.target, ring=ring)
+            for r in range(1, (steps - 1) // 4 + 1):
+                g4.replay()
+                if (4 * r) % 100 == 0:
+                    losses.append(float(g4.loss))
+            for _ in range((steps - 1) % 4):
+                g1.replay()
+        else:
+            g = pkg.StepGraph(model, opt, 64)
+            for i in range(1, steps):
+                g.x.copy_(batches[i % 8][0], non_blocking=True)
+                g.target.copy_(batches[i % 8][1], non_blocking=True)
+                g.replay()
+                if i % 100 == 0:
+                    losses.append(float(g.loss))
         torch.cuda.synchronize()
         finals.append((net.flat_params.clone(), net.flat_grads.clone(), losses))
         model.release_graphs()

@@ -58,24 +58,37 @@ def test_payload_logged_losses_are_the_current_step(tmp_path):
     assert len(set(vals)) > 6 and min(vals) > 0.0
 
 
-def test_step_pipeline_matches_eager_steps():
+@pytest.mark.parametrize("unroll", [1, 4])
+def test_step_pipeline_matches_eager_steps(unroll):
+    """unroll=4: the steps go out four per graph launch; the two left over at the end and a loss somebody reads early
+    go out through the single-step graph.  Either way: the eager trajectory, bit for bit."""
     import pytorch_operator_b200 as pkg
-    batches = [mo.synthetic_batch(64, 300 + i) for i in range(21)]   # more steps than ring slots: slots get reused
+    batches = [mo.synthetic_batch(64, 300 + i) for i in range(23)]   # more steps than ring slots: slots get reused
 
     def run(pipelined):
         torch.manual_seed(1)
         net = pkg.Net().to(DEV)
         opt = pkg.SGD(net.parameters(), lr=0.01, momentum=0.5)
         losses = [float(net.train_step(batches[0][0].to(DEV), batches[0][1].to(DEV), opt))]
-        pipe = pkg.StepPipeline(net, opt, 64) if pipelined else None
-        for x, t in batches[1:]:
+        pipe = pkg.StepPipeline(net, opt, 64, unroll=unroll) if pipelined else None
+        unread = []
+        for k, (x, t) in enumerate(batches[1:]):
             if pipelined:
-                loss = pipe.submit(x.pin_memory(), t.pin_memory())
-                pipe.drain()
-                assert float(loss) == float(pipe.loss_host[(pipe.steps - 1) % pipe.slots])  # stored in pinned host memory by the kernel
+                unread.append(pipe.submit(x.pin_memory(), t.pin_memory()))
+                if unroll == 1:
+                    pipe.drain()
+                    assert float(unread[-1]) == float(pipe.loss_host[(pipe.steps - 1) % pipe.slots])  # stored in pinned host memory by the kernel
+                if k == 9:                      # mid-group read: steps 9 and 10 of the pipeline leave through the single-step graph
+                    float(unread[-1])
+                if len(unread) == 4:            # read before `slots` more steps are submitted
+                    losses += [float(v) for v in unread]
+                    unread = []
             else:
-                loss = net.train_step(x.to(DEV), t.to(DEV), opt)
-            losses.append(float(loss))
+                losses.append(float(net.train_step(x.to(DEV), t.to(DEV), opt)))
+        if pipelined:
+            pipe.drain()
+            losses += [float(v) for v in unread]
+            assert pipe.steps == 22 and int(pipe.ring.state[1]) == 22
         return losses, net.flat_params.clone()
 
     l_e, p_e = run(False)
