@@ -554,7 +554,17 @@ class StepPipeline:
         if self._staged == self.unroll:
             (self.graph_n or self.graph).replay()
             self._staged = 0
+        elif self._device_starving():
+            self.flush()        # nothing is running: grouping would only leave the GPU idle while the group fills
         return StepLoss(self, n)
+
+    def steps_done(self) -> int:
+        """Steps the device has completed on this pipeline's ring (reads the ring's device-side counter: synchronises)."""
+        return int(self.ring.state[1])
+
+    def _device_starving(self) -> bool:
+        launched = self.steps - self._staged
+        return launched == 0 or self.ring.report(launched - 1)[0]
 
     def drain(self):
         self.flush()
