@@ -353,6 +353,8 @@ class Bench:
         same number of times: the step may contain a cross-rank exchange)."""
         torch = self.torch
         sync = sync or torch.cuda.synchronize
+        if SETTLE_S <= 0.0:
+            return 0
         n, t0 = 0, time.time()
         while True:
             for _ in range(64):
@@ -550,7 +552,10 @@ def main():
     ap.add_argument("--profile-iters", type=int, default=30)
     ap.add_argument("--no-config5", action="store_true", help="skip the batch-4096 leg (BASELINE configs[4])")
     ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity prologue (N > 1)")
+    ap.add_argument("--settle", type=float, default=0.3,
+                    help="seconds of untimed load in front of each timed region (0 under ncu, where every launch is replayed)")
     args = ap.parse_args()
+    globals()["SETTLE_S"] = max(0.0, args.settle)
     rank = int(os.environ.get("RANK", 0))
 
     if args.impl == "reference":

@@ -1,3 +1,5 @@
+"""Step time at batch 64 for a list of B200MNIST_PLAN overrides ("fc1_split,dg_split,c2w_split,c2dg_gx", 0 = keep), each in a
+fresh process, UNROLL (default 8) steps per CUDA graph on a resident input ring:  python tools/sweep_plan.py 0,0,0,0 0,0,27,32"""
 import os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 child = r'''
