@@ -427,8 +427,9 @@ class Bench:
         loss_final = float(graph.loss)
 
         # leg 2: end to end from pinned host memory, loss read back every step.  Public API:
-        # StepPipeline.submit(pinned record) = H2D on a copy stream (double-buffered), graph replay, the loss stored
-        # into pinned host memory by the step's last kernel -- all inside the timed region, every step.
+        # StepPipeline.submit(pinned record) = H2D on a copy stream into a slot of a small device ring + the slot's sequence
+        # number behind it, graph replay (the step waits for its slot on the device), {step, loss} stored into pinned host
+        # memory by the step's last kernel -- all inside the timed region, every step.
         pipe = pkg.StepPipeline(model, opt, B, unroll=unroll)
         self.settle(lambda i: pipe.submit(host_ring[i % nhost]), sync=pipe.drain)
         for i in range((W + unroll - 1) // unroll * unroll):

@@ -42,7 +42,7 @@ WORLD_SIZE = int(os.environ.get('WORLD_SIZE', 1))
 
 def train(args, model, device, train_loader, optimizer, epoch, writer):
     """mnist.py:35-49.  Per batch: H2D copy, fused zero_grad/forward/nll_loss/backward/
-    all_reduce/step (double-buffered CUDA-graph replay once the batch shape is known), and the same
+    all_reduce/step (CUDA-graph replays fed through a device ring once the batch shape is known), and the same
     ``loss.item()`` / print / add_scalar every ``log_interval`` batches."""
     model.train()
     graphs = getattr(model, "_b200_step_graphs", None)
