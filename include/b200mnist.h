@@ -84,8 +84,8 @@ int b200mnist_train_step(float *params, float *grads, float *momentum, const flo
  * (replaces the DataLoader + `data.to(device)` of mnist.py:37-38 when the data fits in HBM).
  *   slot s : images at x + s * x_stride floats ([B,1,28,28] fp32, 16-byte aligned), targets at target + s * t_stride
  *   state  : two uint32 in DEVICE memory (8-byte aligned, zero-filled once): [0] the cursor -- the slot the next step
- *            reads -- and [1] the number of steps that have consumed the ring.  conv1's forward kernel reads them, the
- *            step's last kernel sets them to (cursor + 1) % slots and steps + 1.  The host may rewrite the cursor
+ *            reads -- and [1] the number of steps that have consumed the ring.  conv1's forward kernel reads them, one of
+ *            the step's last two kernels sets them to (cursor + 1) % slots and steps + 1.  The host may rewrite the cursor
  *            between steps (stream-ordered).
  * b200mnist_train_step_ring is b200mnist_train_step reading its batch from the ring: `x` and `target` are now OUTPUT
  * buffers of the step ([B,1,28,28] fp32 and int64[B]): the first kernel leaves the slot's batch there for the rest
@@ -95,9 +95,11 @@ int b200mnist_train_step(float *params, float *grads, float *momentum, const flo
  *   landed      : DEVICE uint32: sequence number (1, 2, ...) of the newest batch that has arrived in the ring, written
  *                 BEHIND each copy in copy-stream order (b200mnist_stage_record).  Step n waits on the device until
  *                 landed >= n.
- *   report_host : uint64[slots] in PINNED HOST memory: the last kernel of step n stores (n << 32 | bits of the loss)
- *                 into report_host[slot of step n] as one 8-byte word: when the high half reads n, step n is done, its
- *                 loss is the low half, and the slot may be refilled. */
+ *   report_host : uint64[slots] in PINNED HOST memory: step n stores (n << 32 | bits of the loss) into
+ *                 report_host[slot of step n] as one 8-byte word: when the high half reads n, the loss of step n is
+ *                 final (the low half) and the slot may be refilled.  The store leaves with the step's second-to-last
+ *                 kernel (the parameter update completes right behind it, in stream order), and the cursor / steps
+ *                 pair of `state` advances there too. */
 typedef struct b200mnist_ring {
     const float *x;
     const int64_t *target;

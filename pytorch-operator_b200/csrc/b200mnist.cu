@@ -529,7 +529,8 @@ int launch_conv1_bwd_peer(const float *dp1, const float *p1, const uint8_t *i1, 
     return 0;
 }
 int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
-                     const Plan &pl, cudaStream_t s, const PeerStep *ps = nullptr, bool presignaled = false) {
+                     const Plan &pl, cudaStream_t s, const PeerStep *ps = nullptr, bool presignaled = false,
+                     const LossReduce *early_finish = nullptr) {
     if (ps) {
         switch (ps->pw.world) {
         case 2: return launch_conv1_bwd_peer<2>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
@@ -537,8 +538,13 @@ int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const
         default: return launch_conv1_bwd_peer<8>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
         }
     }
-    CHECK_PDL(launch_pdl(conv1_wgrad_kernel, dim3(pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1, c1w_part, B),
-              "conv1 wgrad", s);
+    if (early_finish)   // host-fed ring: one more grid column closes the step on the ring (loss, cursor, report to the host)
+        CHECK_PDL(launch_pdl(conv1_wgrad_finish_kernel, dim3(pl.c1w_split + 1, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1,
+                             c1w_part, B, *early_finish),
+                  "conv1 wgrad", s);
+    else
+        CHECK_PDL(launch_pdl(conv1_wgrad_kernel, dim3(pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1, c1w_part, B),
+                  "conv1 wgrad", s);
     return 0;
 }
 template <int WORLD>
@@ -594,7 +600,8 @@ int launch_sgd_fused(float *p, float *g, float *m, float lr, float mu, float sca
 // forward (+ optional backward up to the partial gradients)
 int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target, int B, const Workspace &w,
                 const Plan &pl, bool backward, float *logp_out, float *stats_out, float loss_scale, int want_correct,
-                cudaStream_t s, const PeerStep *ps = nullptr, const RingRef *ring = nullptr) {
+                cudaStream_t s, const PeerStep *ps = nullptr, const RingRef *ring = nullptr,
+                const LossReduce *early_finish = nullptr) {
     int rc;
     if ((rc = launch_conv1_fwd(x, P + kOffC1W, P + kOffC1B, w.p1, w.i1, B, s, ring))) return rc;
     // fc1 on the tensor cores reads hi / lo copies of its operands: their producers write them on the way
@@ -636,7 +643,7 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     if ((rc = launch_conv2_bwd(w.dp2_part, pl.dg_split, (size_t)B * kP2Elems, w.p2, w.i2, w.p1, P + kOffC2W, B, w.dp1,
                                w.c2w_part, w.wd, pl, s, pl.c2_presplit, ps ? &sig : nullptr, &sig_sent)))
         return rc;
-    return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s, ps, sig_sent);
+    return launch_conv1_bwd(w.dp1, w.p1, w.i1, x, B, w.c1w_part, pl, s, ps, sig_sent, early_finish);
 }
 
 }  // namespace
@@ -691,12 +698,15 @@ int train_step_impl(float *params, float *grads, float *momentum, const float *x
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const Plan pl = make_plan(B);
     const Workspace w = carve(workspace, B);
+    // a host-fed ring is closed by the conv1 weight-gradient launch (conv1_wgrad_finish_kernel); otherwise the SGD
+    // kernel's last block does it
+    const LossReduce lrd = ring_loss_reduce(w.rows, loss_out, B, ring);
+    const bool early = ring && ring->report_host;
     if ((rc = run_fwd_bwd(params, grads, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s, nullptr,
-                          ring ? &rr : nullptr)))
+                          ring ? &rr : nullptr, early ? &lrd : nullptr)))
         return rc;
     const GradSegments segs = step_segments(w, pl);
-    const LossReduce lrd = ring_loss_reduce(w.rows, loss_out, B, ring);
-    return launch_sgd_fused(params, grads, momentum, lr, mu, 1.0f, first_step, segs, lrd, s);
+    return launch_sgd_fused(params, grads, momentum, lr, mu, 1.0f, first_step, segs, early ? LossReduce{} : lrd, s);
 }
 }  // namespace
 extern "C" {

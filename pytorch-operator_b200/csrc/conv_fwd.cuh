@@ -112,11 +112,16 @@ conv1_relu_pool_fwd_ring_kernel(const RingRef r, const float *__restrict__ w, co
     pdl_wait();
     uint2 st;   // {cursor, steps done}: one 8-byte load, straight from L2
     asm volatile("ld.global.cg.v2.u32 {%0, %1}, [%2];" : "=r"(st.x), "=r"(st.y) : "l"(r.state));
+    unsigned seen = 0;   // host-fed ring: issued right behind the state load, so both are in flight together
+    if (r.landed && threadIdx.x == 0) seen = ld_acquire_sys(r.landed);
     const unsigned slot = st.x;
-    if (r.landed) {   // host-fed ring: the batch of this step may still be on its way (normally it landed long ago)
+    if (r.landed) {   // the batch of this step may still be on its way (normally it landed long ago)
         if (threadIdx.x == 0) {
             SpinClock clk;
-            while ((int)(ld_acquire_sys(r.landed) - (st.y + 1)) < 0) clk.tick();
+            while ((int)(seen - (st.y + 1)) < 0) {
+                clk.tick();
+                seen = ld_acquire_sys(r.landed);
+            }
         }
         __syncthreads();
     }

@@ -1,6 +1,7 @@
 // Gradient finalisation, fused SGD+momentum (mnist.py:140,43) and the smoke-dist square.
 #pragma once
 #include "common.cuh"
+#include "conv_bwd.cuh"
 
 namespace b200mnist {
 
@@ -24,18 +25,20 @@ __device__ __forceinline__ float reduce_partials(const GradSegments &segs, int i
 }
 
 // Deterministic sum of the per-row losses written by head_kernel (and of the per-row "correct"
-// flags when want_correct), by one CTA of 256 threads: strided partial sums, then a fixed tree.
+// flags when want_correct), by the first 256 threads of one CTA: strided partial sums, then a fixed tree.
 __device__ __forceinline__ void reduce_rows_block(const float *rows, int B, float scale, int want_correct,
                                                   float *stats_out) {
     __shared__ float red[256], red2[256];
     const int t = threadIdx.x;
     float s = 0.f, c = 0.f;
-    for (int r = t; r < B; r += 256) {
-        s += __ldcg(rows + r);
-        if (want_correct) c += __ldcg(rows + B + r);
+    if (t < 256) {   // (a larger CTA may call this: its extra threads only take part in the barriers)
+        for (int r = t; r < B; r += 256) {
+            s += __ldcg(rows + r);
+            if (want_correct) c += __ldcg(rows + B + r);
+        }
+        red[t] = s;
+        red2[t] = c;
     }
-    red[t] = s;
-    red2[t] = c;
     __syncthreads();
     for (int o = 128; o > 0; o >>= 1) {
         if (t < o) { red[t] += red[t + o]; red2[t] += red2[t + o]; }
@@ -72,6 +75,22 @@ __device__ __forceinline__ void finish_step(const LossReduce &lr) {
                          "l"(((unsigned long long)done << 32) | (unsigned long long)__float_as_uint(loss)) : "memory");
         }
     }
+}
+
+// conv1's weight gradient with one extra grid column whose first CTA closes the step on a HOST-FED ring early
+// (finish_step: loss, ring bookkeeping, report to the host).  Everything finish_step needs exists since the loss head
+// ran, and only the step's first kernel reads the ring, so nothing has to wait for the SGD kernel -- while the report,
+// a store into host memory, would otherwise sit at the very end of the step, where the kernel boundary waits for it to
+// be acknowledged across PCIe.
+__global__ void __launch_bounds__(kC1wThreads)
+conv1_wgrad_finish_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
+                          const uint8_t *__restrict__ i1, float *__restrict__ part, int B, const LossReduce lr) {
+    pdl_wait();
+    if (blockIdx.x == gridDim.x - 1) {
+        if (blockIdx.y == 0) finish_step(lr);
+        return;
+    }
+    conv1_wgrad_body(x, dp1, p1, i1, part, B, blockIdx.x, gridDim.x - 1, blockIdx.y);
 }
 
 // Writes the summed partials into the flat gradient bucket (the tensors that come out of

@@ -510,7 +510,9 @@ class StepPipeline:
         return (self.ring.report_host & 0xFFFFFFFF).to(torch.int32).view(torch.float32)
 
     def wait_step(self, step: int):
-        """Block the host until step ``step`` (0-based) of this pipeline has completed (spins on pinned memory)."""
+        """Block the host until step ``step`` (0-based) of this pipeline has reported to pinned host memory: its loss is
+        final and its ring slot may be refilled (the report leaves with the step's second-to-last kernel; the SGD
+        update completes right behind it, in stream order -- ``drain()`` or any stream-ordered read waits for that)."""
         if step >= self.steps - self._staged:
             self.flush()
         while not self.ring.report(step)[0]:
