@@ -519,12 +519,13 @@ struct PeerStep {
 };
 template <int WORLD>
 int launch_conv1_bwd_peer(const float *dp1, const float *p1, const uint8_t *i1, const float *x, int B, float *c1w_part,
-                          const Plan &pl, const PeerStep &ps, bool presignaled, cudaStream_t s) {
+                          const Plan &pl, const PeerStep &ps, bool presignaled, cudaStream_t s, const LossReduce *early) {
     // exchange CTAs: one float4 of this rank's fc1 slice per thread, an even count split over the two grid rows
     constexpr int per = (kFc1Vec4 + WORLD - 1) / WORLD;
     const int nx = ceil_div(ceil_div(per, kC1wThreads), 2);
-    CHECK_PDL(launch_pdl(conv1_wgrad_peer_kernel<WORLD>, dim3(nx + pl.c1w_split, 2), dim3(kC1wThreads), 0, s, x, dp1, p1, i1,
-                         c1w_part, B, ps.pw, ps.m, ps.parity, ps.neg_lr, ps.mu, ps.scale, ps.first, nx, presignaled ? 1 : 0),
+    CHECK_PDL(launch_pdl(conv1_wgrad_peer_kernel<WORLD>, dim3(nx + pl.c1w_split + (early ? 1 : 0), 2), dim3(kC1wThreads), 0, s,
+                         x, dp1, p1, i1, c1w_part, B, ps.pw, ps.m, ps.parity, ps.neg_lr, ps.mu, ps.scale, ps.first, nx,
+                         presignaled ? 1 : 0, early ? *early : LossReduce{}, early ? 1 : 0),
               "conv1 wgrad + fc1 slice exchange (reduce + sgd + push over NVLink)", s);
     return 0;
 }
@@ -533,9 +534,9 @@ int launch_conv1_bwd(const float *dp1, const float *p1, const uint8_t *i1, const
                      const LossReduce *early_finish = nullptr) {
     if (ps) {
         switch (ps->pw.world) {
-        case 2: return launch_conv1_bwd_peer<2>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
-        case 4: return launch_conv1_bwd_peer<4>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
-        default: return launch_conv1_bwd_peer<8>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s);
+        case 2: return launch_conv1_bwd_peer<2>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s, early_finish);
+        case 4: return launch_conv1_bwd_peer<4>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s, early_finish);
+        default: return launch_conv1_bwd_peer<8>(dp1, p1, i1, x, B, c1w_part, pl, *ps, presignaled, s, early_finish);
         }
     }
     if (early_finish)   // host-fed ring: one more grid column closes the step on the ring (loss, cursor, report to the host)
@@ -843,16 +844,19 @@ int peer_train_step_impl(void *const *windows_host, int rank, int world_size, in
     const Plan pl = make_plan(B);
     const Workspace w = carve(workspace, B);
     // forward, loss head, fc backward (fc1's gradient lands in this step's staging bucket), conv2 backward, then conv1's
-    // weight gradient with the fc1 slice exchange in the same launch
+    // weight gradient with the fc1 slice exchange in the same launch (which also closes a host-fed ring, see
+    // conv1_wgrad_finish_kernel)
+    const LossReduce lrd = ring_loss_reduce(w.rows, loss_out, B, ring);
+    const bool early = ring && ring->report_host;
     if ((rc = run_fwd_bwd(params, staging, x, target, B, w, pl, true, nullptr, loss_out, 1.0f / (float)B, 0, s, &ps,
-                          ring ? &rr : nullptr)))
+                          ring ? &rr : nullptr, early ? &lrd : nullptr)))
         return rc;
     const GradSegments segs = step_segments(w, pl);
-    const LossReduce lrd = ring_loss_reduce(w.rows, loss_out, B, ring);
+    const LossReduce tail_lrd = early ? LossReduce{} : lrd;
     switch (world_size) {
-    case 2: return launch_peer_tail<2>(ps, segs, lrd, s);
-    case 4: return launch_peer_tail<4>(ps, segs, lrd, s);
-    default: return launch_peer_tail<8>(ps, segs, lrd, s);
+    case 2: return launch_peer_tail<2>(ps, segs, tail_lrd, s);
+    case 4: return launch_peer_tail<4>(ps, segs, tail_lrd, s);
+    default: return launch_peer_tail<8>(ps, segs, tail_lrd, s);
     }
 }
 }  // namespace

@@ -171,13 +171,17 @@ __global__ void __launch_bounds__(kC1wThreads)
 conv1_wgrad_peer_kernel(const float *__restrict__ x, const float *__restrict__ dp1, const float *__restrict__ p1,
                         const uint8_t *__restrict__ i1, float *__restrict__ part, int B,
                         const __grid_constant__ PeerWin pw, float *__restrict__ m, int parity, float neg_lr, float mu,
-                        float scale, int first_step, int nx, int presignaled) {
+                        float scale, int first_step, int nx, int presignaled, const LossReduce early, int n_early) {
     pdl_wait();
+    if (n_early && blockIdx.x == gridDim.x - 1) {   // host-fed ring: one more grid column closes the step on the ring early
+        if (blockIdx.y == 0) finish_step(early);    // (see conv1_wgrad_finish_kernel, optim.cuh)
+        return;
+    }
     if ((int)blockIdx.x < nx)
         peer_fc1_slice<WORLD>(pw, m, parity, neg_lr, mu, scale, first_step, blockIdx.y * nx + blockIdx.x, 2 * nx,
                               presignaled);
     else
-        conv1_wgrad_body(x, dp1, p1, i1, part, B, blockIdx.x - nx, gridDim.x - nx, blockIdx.y);
+        conv1_wgrad_body(x, dp1, p1, i1, part, B, blockIdx.x - nx, gridDim.x - nx - n_early, blockIdx.y);
 }
 
 // The end of the step (replaces grad_finalize + all_reduce + optimizer.step()): blocks [0, kFusedCovBlocks) own one
