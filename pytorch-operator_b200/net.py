@@ -513,6 +513,8 @@ class StepPipeline:
         """Block the host until step ``step`` (0-based) of this pipeline has reported to pinned host memory: its loss is
         final and its ring slot may be refilled (the report leaves with the step's second-to-last kernel; the SGD
         update completes right behind it, in stream order -- ``drain()`` or any stream-ordered read waits for that)."""
+        if not 0 <= step < self.steps:
+            raise IndexError(f"step {step} has not been submitted ({self.steps} so far)")
         if step >= self.steps - self._staged:
             self.flush()
         while not self.ring.report(step)[0]:
