@@ -84,7 +84,7 @@ class InputRing:
 
     def report(self, step: int):
         """Host-fed rings: (done, loss) of 0-based step ``step`` as last reported to pinned host memory by the step's
-        last kernel (one 8-byte word: no CUDA call, no tearing).  ``done`` turns True when the step has completed;
+        second-to-last kernel (one 8-byte word: no CUDA call, no tearing).  ``done`` turns True when the step has reported;
         ``loss`` is None once the slot has been reused by a later step."""
         word = self._report[step % self.slots]
         seq = word >> 32
@@ -446,7 +446,7 @@ class StepGraph:
 
 
 class StepLoss:
-    """What ``StepPipeline.submit`` returns: the loss of the step just enqueued.  The step's last kernel stores it
+    """What ``StepPipeline.submit`` returns: the loss of the step just enqueued.  The step stores it
     in pinned host memory asynchronously, so reading it means waiting for THAT step -- ``item()`` (what
     mnist.py:47 calls) and ``float()`` wait until the step has reported completion to the host first, like
     ``loss.item()`` on a CUDA tensor does in the reference.  Read it before ``slots`` more steps are submitted."""
@@ -472,7 +472,7 @@ class StepPipeline:
     pinned host batch of step n into slot n % slots on a COPY stream and writes the slot's sequence number behind the
     copy (a stream memory operation, ``b200mnist_stage_record``), then replays the step's CUDA graph.  The step's
     first kernel waits ON THE DEVICE until its slot carries its sequence number (normally it has for a long time: the
-    copies run ahead of the steps) and its last kernel stores the loss and the step count into pinned host memory,
+    copies run ahead of the steps) and its second-to-last kernel stores the loss and the step count into pinned host memory
     (one 8-byte word), which is how the host knows a slot may be refilled and a loss may be read -- no event, no stream
     wait, no copy node between two replays.
 
