@@ -250,3 +250,40 @@ def test_ddp_worker_batches_are_the_oracles():
     for seed in (0, 1234, 9001):
         a, b = dw.synthetic_batch(64, seed), mo.synthetic_batch(64, seed)
         assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def test_bench_clock_summary_of_a_region_shorter_than_the_sampling_period():
+    """bench.py: with the driver's --steps 20 the timed region lasts ~1 ms, shorter than nvidia-smi's 50 ms sampling
+    period; the clock block then reports the samples of the untimed load phase directly before the region and says so
+    (a long region reports its own samples and carries no note); throttle reasons are collected either way."""
+    sys.path.insert(0, ROOT)
+    import bench
+    s = bench.ClockSampler.__new__(bench.ClockSampler)
+    row = "1965, 1965, 600.0, Not Active, Not Active, Not Active, {}"
+    s.rows = [(100.00 + 0.05 * i, row.format("Active" if i == 6 else "Not Active")) for i in range(10)]   # t = 100.00 .. 100.45
+    short = s.under_load(100.452, 100.453)            # no sample inside; the load phase before it has several
+    assert short["samples"] >= 5 and short["sm_mhz"] == 1965.0 and "shorter than the 50 ms sampling period" in short["note"]
+    assert short["reasons"] == ["sw_power_cap"]
+    long = s.under_load(100.0, 100.45)
+    assert long["samples"] == 10 and "note" not in long
+    s.rows = []
+    assert s.under_load(1.0, 2.0) is None               # nvidia-smi missing: no clock block rather than a made-up one
+
+
+def test_ring_description_and_ring_entry_points_reject_bad_arguments_without_a_gpu():
+    """b200mnist_train_step_ring validates the ring description before anything is launched."""
+    L = _cabi.lib()
+    n = int(L.b200mnist_flat_elems())
+    buf = np.zeros(n + 64, dtype=np.float32)
+    base = (buf.ctypes.data + 255) // 256 * 256
+    ws_bytes = int(L.b200mnist_workspace_bytes(4))
+    ws = np.zeros(ws_bytes + 256, dtype=np.uint8)
+    wsp = (ws.ctypes.data + 255) // 256 * 256
+    call = lambda ring: L.b200mnist_train_step_ring(base, base, base, ring, base, base, 4, wsp, ws_bytes, 0.01, 0.5, 1, base, None)
+    assert call(None) < 0 and "ring" in _cabi.last_error()
+    ring = _cabi.Ring(base, base, 4 * 784, 4, 0, base, None, None)          # no slots
+    assert call(ctypes.byref(ring)) < 0 and "slot" in _cabi.last_error()
+    ring = _cabi.Ring(base, base, 4 * 784 - 1, 4, 2, base, None, None)      # slots overlap / misaligned stride
+    assert call(ctypes.byref(ring)) < 0 and "aligned" in _cabi.last_error()
+    ring = _cabi.Ring(base, base, 4 * 784, 4, 2, None, None, None)          # no cursor
+    assert call(ctypes.byref(ring)) < 0 and "null" in _cabi.last_error()
