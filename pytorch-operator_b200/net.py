@@ -234,7 +234,7 @@ class Net(nn.Module):
         ws = self.workspace(B)
         L = _cabi.lib()
         lo = self._loss if loss_out is None else loss_out
-        gr = self.flat_grads if grads_out is None else grads_out  # e.g. DDP's symmetric staging bucket
+        gr = self.flat_grads if grads_out is None else grads_out  # e.g. the staging bucket of DDP's peer window
         _cabi.check(L.b200mnist_forward_backward(self.flat_params.data_ptr(), gr.data_ptr(),
                                                  x.data_ptr(), target.data_ptr(), B, ws.data_ptr(), ws.numel(),
                                                  lo.data_ptr(), _cabi.ptr(logp_out), _stream()),
