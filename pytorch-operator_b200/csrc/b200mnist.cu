@@ -625,7 +625,7 @@ int run_fwd_bwd(const float *P, float *G, const float *x, const int64_t *target,
     // bucket) start from zero (see fc1_bwd_tc_kernel)
     const HeadTcExtra hx{ops.dz1_hi, ops.dz1_lo, reinterpret_cast<float4 *>(G + kOffF1W), (kOffF2W - kOffF1W) / 4};
     a.rows = w.rows; a.ticket = w.ticket; a.stats_out = stats_out;
-    a.defer_reduce = backward ? 1 : 0;  // training: the step's last kernel reduces the per-row losses
+    a.defer_reduce = backward ? 1 : 0;  // training: a later kernel of the step reduces the per-row losses (finish_step)
     a.B = B; a.nsplit = nsplit; a.want_correct = want_correct; a.inv_B = 1.0f / (float)B; a.loss_scale = loss_scale;
     if ((rc = launch_head(a, s, fc1_bwd_tc ? &hx : nullptr))) return rc;
     if (!backward) return 0;

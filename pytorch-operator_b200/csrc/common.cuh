@@ -60,7 +60,8 @@ __device__ __forceinline__ void send_early_signal(const EarlySignal &sig) {
 // "Resident input": a ring of batches that already sits in device memory plus a device-side cursor, so that a
 // CUDA-graph replay of the step needs no copy and no host-side pointer: conv1's forward kernel reads slot *cursor
 // (x + slot * x_stride floats, target + slot * t_stride elements), leaves copies in the step's ordinary input buffers
-// (x_copy / t_copy: what the later kernels of the step read) and the step's last kernel advances the cursor.
+// (x_copy / t_copy: what the later kernels of the step read) and the end of the step advances the cursor (finish_step:
+// the SGD kernel's last block, or one CTA of the conv1 weight-gradient launch on a host-fed ring).
 // Host-fed rings (a copy stream refills the slots while the steps run): `landed` holds the sequence number of the
 // newest batch that has arrived (written behind each copy, in copy-stream order) and state[1] counts the steps that
 // have consumed the ring, so step n (1-based) waits until landed >= n -- on the device, which is what lets the

@@ -104,7 +104,7 @@ conv1_relu_pool_fwd_kernel(const float *__restrict__ x, const float *__restrict_
     conv1_fwd_body<false>(x, w, bias, out, idx, B, nullptr);
 }
 
-// The same from a resident ring (RingRef): the cursor is read after the previous step's last kernel, which advanced
+// The same from a resident ring (RingRef): the cursor is read after the previous step, whose finish_step advanced
 // it, has completed; CTA (b, 0) also forwards target b.
 __global__ void __launch_bounds__(kC1Threads)
 conv1_relu_pool_fwd_ring_kernel(const RingRef r, const float *__restrict__ w, const float *__restrict__ bias,

@@ -60,7 +60,8 @@ struct LossReduce {   // rows == nullptr: nothing to do
     unsigned slots;
     unsigned long long *report_host;    // host-fed rings: report_host[slot] (PINNED HOST memory) = {step number, loss bits}
 };
-// Last block of the step's last kernel: the scalar loss, then the ring bookkeeping.  The report to the host is ONE
+// End of the step (the SGD kernel's last block, or one CTA of the conv1 weight-gradient launch on a host-fed ring, or
+// the last block of the fused DDP tail): the scalar loss, then the ring bookkeeping.  The report to the host is ONE
 // 8-byte store (sequence number in the high word, the loss in the low one): the host sees both or neither, so no
 // system-scope fence has to order a "done" flag behind the loss at the very end of the step.
 __device__ __forceinline__ void finish_step(const LossReduce &lr) {
